@@ -1,0 +1,88 @@
+/*
+ * janus_b200.h -- C ABI of libjanus_b200.so (hand-written sm_100a CUDA kernels for the
+ * sender-side semantic-encode path of akshatvasisht/janus).
+ *
+ * Conventions
+ *   - every entry point is extern "C", returns int32 status: 0 = OK, <0 = janus_status_t error;
+ *     janus_last_error() returns a thread-local, human-readable message for the last failure.
+ *   - all tensor arguments are DEVICE pointers owned by the caller (no torch types); shapes are
+ *     explicit; `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - the library allocates nothing persistent and never synchronises the host, except for the
+ *     *_host convenience entry points which say so.
+ *   - native code never calls abort()/exit(); the Python service layer turns a non-zero status
+ *     into an ordinary Python exception, which is the error contract the reference's callers
+ *     rely on (/root/reference/backend/services/engine.py:513-525).
+ *
+ * What each entry point replaces in the reference (paths relative to /root/reference):
+ *   janus_yin_frames_f32      aubio.pitch('yin',4096,hop,sr) called once per hop
+ *                             backend/services/prosody.py:32-34 (ctor), :76-87 (hop loop);
+ *                             upstream aubio 0.4.9 src/pitch/pitch.c + pitchyin.c + mathutils.c
+ *   janus_prosody_reduce_f32  backend/services/prosody.py:67 (RMS), :69-74 (energy tag),
+ *                             :86-99 (voiced filter, np.mean, pitch tag)
+ *   janus_yin_state_f32       the stateful sliding buffer inside the aubio object
+ *                             (prosody.py:32; aubio_pitch_slideblock)
+ */
+#ifndef JANUS_B200_H
+#define JANUS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define JANUS_ABI_VERSION 1
+
+typedef enum {
+  JANUS_OK = 0,
+  JANUS_ERR_INVALID_ARG = -1,  /* bad shape / unsupported parameter combination */
+  JANUS_ERR_CUDA = -2,         /* a CUDA runtime call or launch failed           */
+  JANUS_ERR_UNSUPPORTED = -3,  /* device is not sm_100 / feature not built       */
+  JANUS_ERR_WORKSPACE = -4     /* caller-provided workspace too small            */
+} janus_status_t;
+
+int32_t janus_abi_version(void);
+const char* janus_last_error(void);
+/* 0 when device `dev` can run the kernels (compute capability 10.x), else JANUS_ERR_UNSUPPORTED. */
+int32_t janus_check_device(int32_t dev);
+
+/* ------------------------------------------------------------------------------------------
+ * K4: YIN pitch + per-hop level (bit-exact restatement of aubio's float32 arithmetic)
+ * ------------------------------------------------------------------------------------------
+ * Streams are concatenated in `pcm`; stream s occupies pcm[stream_offsets[s] .. +stream_lengths[s]).
+ * n_hops(s) = ceil(len/hop); hop_offsets[s] = sum_{t<s} n_hops(t) (n_streams+1 entries).
+ * Frames of a stream are processed in groups of janus_yin_frames_per_group() consecutive hops
+ * by one thread block; group_offsets[s] = sum_{t<s} ceil(n_hops(t)/F) (n_streams+1 entries).
+ * state_in: [n_streams, buf_size] previous sliding buffers, or NULL for fresh (all-zero) state.
+ * Outputs (all [total_hops]): f0_out in Hz (0 = unvoiced / gated), hop_db_out = 10*log10(mean(x^2))
+ * of the hop (aubio_db_spl), hop_sumsq_out = sum(x^2) of the hop (for the stream RMS).
+ * Constraints: buf_size % 512 == 0, hop_size % 4 == 0, hop_size <= buf_size.
+ */
+int32_t janus_yin_frames_per_group(void);
+int32_t janus_yin_frames_f32(const float* pcm, const int64_t* stream_offsets,
+                             const int64_t* stream_lengths, const int64_t* hop_offsets,
+                             const int32_t* group_offsets, int32_t n_streams, int64_t total_groups,
+                             int32_t sample_rate, int32_t buf_size, int32_t hop_size,
+                             float tolerance, float silence_db, const float* state_in,
+                             float* f0_out, float* hop_db_out, float* hop_sumsq_out, void* stream);
+
+/* New sliding-buffer state after the call above: state_out[s] = last buf_size samples of
+ * (state_in[s] ++ zero-padded stream s). state_out must not alias state_in. */
+int32_t janus_yin_state_f32(const float* pcm, const int64_t* stream_offsets,
+                            const int64_t* stream_lengths, int32_t n_streams, int32_t buf_size,
+                            int32_t hop_size, const float* state_in, float* state_out, void* stream);
+
+/* Per-stream reduction: rms_out[s] = sqrt(sum(x^2)/len); mean_f0_out[s] = float32 mean of the
+ * voiced (f0 > 0) hops in numpy's pairwise summation order (bit-identical to np.mean of the
+ * float32 list at prosody.py:90), 0 when no hop is voiced; n_voiced_out[s]; tags_out[2*s+0] =
+ * energy tag (0 Quiet, 1 Normal, 2 Loud), tags_out[2*s+1] = pitch tag (0 Deep, 1 Normal, 2 High).
+ * scratch: [total_hops] floats. */
+int32_t janus_prosody_reduce_f32(const float* f0, const float* hop_sumsq, const int64_t* hop_offsets,
+                                 const int64_t* stream_lengths, int32_t n_streams, float* scratch,
+                                 float* rms_out, float* mean_f0_out, int32_t* n_voiced_out,
+                                 uint8_t* tags_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* JANUS_B200_H */

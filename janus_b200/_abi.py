@@ -1,0 +1,80 @@
+"""ctypes binding of libjanus_b200.so (the C ABI declared in include/janus_b200.h).
+
+No torch types cross this boundary: callers pass `tensor.data_ptr()` integers, explicit sizes and
+the raw cudaStream_t handle. A non-zero status becomes a Python exception (the reference's callers
+catch ordinary exceptions: /root/reference/backend/services/engine.py:513-525).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "libjanus_b200.so")
+
+_c = ctypes
+_P = _c.c_void_p
+_I32 = _c.c_int32
+_I64 = _c.c_int64
+_F32 = _c.c_float
+
+# name -> (restype, argtypes); must list every symbol include/janus_b200.h declares.
+SIGNATURES = {
+    "janus_abi_version": (_I32, []),
+    "janus_last_error": (_c.c_char_p, []),
+    "janus_check_device": (_I32, [_I32]),
+    "janus_yin_frames_per_group": (_I32, []),
+    "janus_yin_frames_f32": (_I32, [_P, _P, _P, _P, _P, _I32, _I64, _I32, _I32, _I32, _F32, _F32,
+                                    _P, _P, _P, _P, _P]),
+    "janus_yin_state_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
+    "janus_prosody_reduce_f32": (_I32, [_P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P]),
+}
+
+
+class JanusNativeError(RuntimeError):
+    """Raised when a libjanus_b200 entry point returns a non-zero status."""
+
+
+_lib = None
+_lock = threading.Lock()
+
+
+def lib() -> ctypes.CDLL:
+    """Loads libjanus_b200.so, building it with nvcc first if it is missing or stale.
+
+    There is no fallback: if the library cannot be built or loaded this raises.
+    """
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            from . import build as _build
+            try:
+                _build.build()
+            except Exception as exc:  # noqa: BLE001
+                raise JanusNativeError(
+                    f"libjanus_b200.so is missing and could not be built with nvcc: {exc}. "
+                    "Run `python -m janus_b200.build`. There is no CPU fallback.") from exc
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        if L.janus_abi_version() != 1:
+            raise JanusNativeError("libjanus_b200.so ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        msg = lib().janus_last_error()
+        raise JanusNativeError(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+
+
+def call(name: str, *args) -> None:
+    check(getattr(lib(), name)(*args), name)
