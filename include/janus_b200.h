@@ -82,6 +82,21 @@ int32_t janus_prosody_reduce_f32(const float* f0, const float* hop_sumsq, const 
                                  float* rms_out, float* mean_f0_out, int32_t* n_voiced_out,
                                  uint8_t* tags_out, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * K2 building block: bf16 GEMM on tcgen05/TMEM fed by TMA, fused epilogue
+ * ------------------------------------------------------------------------------------------
+ * out[b, t + out_row_offset, n] = act( sum_k A[b, t, k] * W[n, k] + bias[n] ) + pos[t, n] + residual[b, t, n]
+ * A: bf16, row t of batch b at A + b*a_batch_stride + t*lda (elements; rows may overlap: this is how
+ * the conv1d stem layers are expressed), W: bf16 [N, K] with leading dimension ldw, out/residual bf16
+ * with leading dimension ldc and batch stride out_batch_stride, bias fp32 [N] or NULL, pos fp32
+ * [M_per_batch, N] or NULL, act 0 = none / 1 = exact (erf) GELU. N % 64 == 0; K, lda, ldw, ldc % 8 == 0.
+ * Replaces the int8/fp32 CPU GEMMs inside CTranslate2's Whisper.encode that the reference reaches via
+ * backend/services/transcriber.py:53-57. */
+int32_t janus_gemm_bf16(const void* A, int64_t lda, int64_t a_batch_stride, const void* W, int64_t ldw,
+                        void* out, int64_t ldc, int64_t out_batch_stride, int32_t out_row_offset,
+                        int32_t M_per_batch, int32_t n_batch, int32_t N, int32_t K, const float* bias,
+                        const void* residual, const float* pos, int32_t act, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,6 +29,8 @@ SIGNATURES = {
                                     _P, _P, _P, _P, _P]),
     "janus_yin_state_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     "janus_prosody_reduce_f32": (_I32, [_P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P]),
+    "janus_gemm_bf16": (_I32, [_P, _I64, _I64, _P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32,
+                               _P, _P, _P, _I32, _P]),
 }
 
 

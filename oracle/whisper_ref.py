@@ -1,0 +1,191 @@
+"""CPU oracle for Whisper STT (encoder, KV-cache decoder, greedy decode) -- TEST INFRASTRUCTURE ONLY.
+
+fp32 PyTorch restatement of what the reference reaches through
+`WhisperModel(...).transcribe(audio_16k, beam_size=1, language='en')`
+(/root/reference/backend/services/transcriber.py:23-27,53-57). The arithmetic lives in the
+un-vendored third-party packages faster-whisper (>=1.0.0, requirements.txt:2) -> CTranslate2; what is
+restated here is the published OpenAI Whisper architecture those packages execute and the decode-time
+logit rules of faster-whisper's `generate_with_fallback` at temperature 0 / beam_size 1:
+suppress_blank, suppress_tokens=[-1] (non-speech set + specials), timestamp rules with
+max_initial_timestamp_index=50, max_length 448.
+
+PARITY UNPINNED against faster-whisper/CTranslate2 (not installable offline; the reference's tests mock
+the model). Cross-checked against the independent HF `transformers` Whisper implementation in
+tests/test_oracle_stt.py (same weights, fp32, encoder states and teacher-forced logits).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+from janus_b200.whisper.config import TokenizerSpec, WhisperDims
+
+
+def _ln(x, W, p):
+    return F.layer_norm(x, (x.shape[-1],), W[p + ".w"], W[p + ".b"], eps=1e-5)
+
+
+def _lin(x, W, p):
+    return F.linear(x, W[p + ".w"], W.get(p + ".b"))
+
+
+def _mha(xq, xkv, W, p, n_head, mask=None, kv=None):
+    """Whisper MultiHeadAttention: scale d_h**-0.25 on both q and k. kv = precomputed (k, v)."""
+    q = _lin(xq, W, p + ".q")
+    if kv is None:
+        k, v = _lin(xkv, W, p + ".k"), _lin(xkv, W, p + ".v")
+    else:
+        k, v = kv
+    B, Tq, D = q.shape
+    dh = D // n_head
+    scale = dh ** -0.25
+    qh = (q.view(B, Tq, n_head, dh).permute(0, 2, 1, 3)) * scale
+    kh = (k.view(B, -1, n_head, dh).permute(0, 2, 3, 1)) * scale
+    vh = v.view(B, -1, n_head, dh).permute(0, 2, 1, 3)
+    s = qh @ kh
+    if mask is not None:
+        s = s + mask
+    w = torch.softmax(s.float(), dim=-1)
+    o = (w @ vh).permute(0, 2, 1, 3).reshape(B, Tq, D)
+    return _lin(o, W, p + ".o"), (k, v)
+
+
+def encode(W, dims: WhisperDims, mel: torch.Tensor, taps: dict | None = None) -> torch.Tensor:
+    """mel: [B, n_mels, 2*n_audio_ctx] fp32 -> [B, n_audio_ctx, d]."""
+    x = F.gelu(F.conv1d(mel, W["enc.conv1.w"], W["enc.conv1.b"], padding=1))
+    if taps is not None:
+        taps["conv1"] = x.permute(0, 2, 1)
+    x = F.gelu(F.conv1d(x, W["enc.conv2.w"], W["enc.conv2.b"], stride=2, padding=1))
+    x = x.permute(0, 2, 1) + W["enc.pos"]
+    if taps is not None:
+        taps["conv2"] = x
+    for i in range(dims.n_audio_layer):
+        p = f"enc.l{i}"
+        h = _ln(x, W, p + ".attn_ln")
+        a, _ = _mha(h, h, W, p + ".attn", dims.n_audio_head)
+        x = x + a
+        h = _lin(F.gelu(_lin(_ln(x, W, p + ".mlp_ln"), W, p + ".mlp.fc1")), W, p + ".mlp.fc2")
+        x = x + h
+        if taps is not None:
+            taps[f"l{i}"] = x
+    return _ln(x, W, "enc.ln_post")
+
+
+class DecoderState:
+    """Self-attention KV cache + per-layer cross K/V (computed once per window)."""
+
+    def __init__(self, W, dims: WhisperDims, enc_out: torch.Tensor):
+        self.W, self.dims = W, dims
+        self.cross = []
+        for i in range(dims.n_text_layer):
+            p = f"dec.l{i}.cross"
+            self.cross.append((_lin(enc_out, W, p + ".k"), _lin(enc_out, W, p + ".v")))
+        self.self_kv = [None] * dims.n_text_layer
+        self.offset = 0
+
+    def step(self, tokens: torch.Tensor) -> torch.Tensor:
+        """tokens: [B, T_new] -> logits [B, T_new, V] (fp32), appending to the cache."""
+        W, dims = self.W, self.dims
+        T = tokens.shape[1]
+        x = W["dec.tok_emb"][tokens] + W["dec.pos"][self.offset:self.offset + T]
+        total = self.offset + T
+        mask = torch.full((T, total), float("-inf")).triu_(self.offset + 1)
+        for i in range(dims.n_text_layer):
+            p = f"dec.l{i}"
+            h = _ln(x, W, p + ".attn_ln")
+            k_new, v_new = _lin(h, W, p + ".attn.k"), _lin(h, W, p + ".attn.v")
+            if self.self_kv[i] is not None:
+                k_all = torch.cat([self.self_kv[i][0], k_new], 1)
+                v_all = torch.cat([self.self_kv[i][1], v_new], 1)
+            else:
+                k_all, v_all = k_new, v_new
+            self.self_kv[i] = (k_all, v_all)
+            a, _ = _mha(h, None, W, p + ".attn", dims.n_text_head, mask=mask, kv=(k_all, v_all))
+            x = x + a
+            c, _ = _mha(_ln(x, W, p + ".cross_ln"), None, W, p + ".cross", dims.n_text_head, kv=self.cross[i])
+            x = x + c
+            x = x + _lin(F.gelu(_lin(_ln(x, W, p + ".mlp_ln"), W, p + ".mlp.fc1")), W, p + ".mlp.fc2")
+        self.offset = total
+        x = _ln(x, W, "dec.ln")
+        return (x @ W["dec.tok_emb"].T).float()
+
+
+def apply_logit_rules(logits: torch.Tensor, generated: list[int], spec: TokenizerSpec,
+                      suppress_mask: torch.Tensor) -> torch.Tensor:
+    """One sequence. `generated` = tokens sampled so far (after the sot prompt). Returns filtered
+    logits (-inf = forbidden). Order follows faster-whisper / openai-whisper: SuppressBlank,
+    SuppressTokens, ApplyTimestampRules."""
+    lg = logits.clone()
+    ninf = float("-inf")
+    tb = spec.timestamp_begin
+    if len(generated) == 0:                       # SuppressBlank at sample_begin
+        lg[spec.blank] = ninf
+        lg[spec.eot] = ninf
+    lg[suppress_mask] = ninf                       # SuppressTokens (+ <|notimestamps|>)
+    last_ts = len(generated) >= 1 and generated[-1] >= tb
+    penult_ts = len(generated) < 2 or generated[-2] >= tb
+    if last_ts:
+        if penult_ts:
+            lg[tb:] = ninf                         # must be non-timestamp
+        else:
+            lg[:spec.eot] = ninf                   # cannot be a normal text token
+    ts = [t for t in generated if t >= tb]
+    if ts:
+        ts_last = ts[-1] if (last_ts and not penult_ts) else ts[-1] + 1
+        lg[tb:ts_last] = ninf                      # timestamps never decrease
+    if len(generated) == 0:
+        lg[:tb] = ninf                             # first token must be a timestamp ...
+        lg[tb + spec.max_initial_timestamp_index + 1:] = ninf   # ... no later than 1.0 s
+    lp = torch.log_softmax(lg.float(), dim=-1)
+    ts_lp = torch.logsumexp(lp[tb:], dim=-1)
+    max_text = lp[:tb].max()
+    if ts_lp > max_text:
+        lg[:tb] = ninf
+    return lg
+
+
+def suppress_mask_for(spec: TokenizerSpec) -> torch.Tensor:
+    m = torch.zeros(spec.n_vocab, dtype=torch.bool)
+    m[list(spec.suppress_ids)] = True
+    return m
+
+
+def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor, max_new_tokens: int,
+                  stop_at_eot: bool = True, return_margins: bool = False):
+    """Batched greedy decode at temperature 0. Returns tokens [B, max_new_tokens] (eot-padded after
+    the first eot), sum of log-probs [B], and optionally the top-1/top-2 margin at every step."""
+    B = enc_out.shape[0]
+    st = DecoderState(W, dims, enc_out)
+    sup = suppress_mask_for(spec)
+    prompt = torch.tensor([list(spec.sot_sequence)] * B, dtype=torch.long)
+    logits = st.step(prompt)[:, -1]
+    gen = [[] for _ in range(B)]
+    done = [False] * B
+    out = torch.full((B, max_new_tokens), spec.eot, dtype=torch.long)
+    sum_lp = torch.zeros(B)
+    margins = torch.full((B, max_new_tokens), float("inf"))
+    n_steps = min(max_new_tokens, spec.max_length - len(spec.sot_sequence))
+    for t in range(n_steps):
+        nxt = torch.full((B,), spec.eot, dtype=torch.long)
+        for b in range(B):
+            if done[b]:
+                continue
+            lg = apply_logit_rules(logits[b], gen[b], spec, sup)
+            lp = torch.log_softmax(lg, dim=-1)
+            top2 = torch.topk(lg, 2)
+            tok = int(top2.indices[0])
+            margins[b, t] = float(top2.values[0] - top2.values[1])
+            nxt[b] = tok
+            out[b, t] = tok
+            sum_lp[b] += lp[tok]
+            gen[b].append(tok)
+            if tok == spec.eot and stop_at_eot:
+                done[b] = True
+        if all(done) or t == n_steps - 1:
+            break
+        logits = st.step(nxt[:, None])[:, -1]
+    if return_margins:
+        return out, sum_lp, margins
+    return out, sum_lp
