@@ -97,6 +97,60 @@ int32_t janus_gemm_bf16(const void* A, int64_t lda, int64_t a_batch_stride, cons
                         int32_t M_per_batch, int32_t n_batch, int32_t N, int32_t K, const float* bias,
                         const void* residual, const float* pos, int32_t act, void* stream);
 
+/* Building blocks exposed for parity tests (same kernels the encoder driver launches). */
+int32_t janus_layernorm_bf16(const void* x, const float* w, const float* b, void* y, int64_t rows, int32_t d,
+                             void* stream);
+/* Fused non-causal attention over packed qkv bf16 [n_batch, T, 3*64*n_heads] -> out bf16 [n_batch, T, 64*n_heads]. */
+int32_t janus_attention_enc_bf16(const void* qkv, void* out, int32_t n_batch, int32_t T, int32_t n_heads,
+                                 void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K1: batched log-mel frontend (replaces faster_whisper FeatureExtractor + pad_or_trim; fuses the
+ * reference's audio[::3] decimation, backend/services/transcriber.py:51, as decim = 3)
+ * ------------------------------------------------------------------------------------------
+ * Utterance s = pcm[offsets[s] .. +lengths[s]) at the SOURCE rate; the frontend sees x[::decim].
+ * Utterances longer than one 30 s window are clipped to the first window (the host splits them).
+ * mel_start/mel_len/mel_w: the Slaney filterbank in sparse row form (row m covers bins
+ * [mel_start[m], mel_start[m]+mel_len[m]) with weights mel_w[m*mel_max_len + j]).
+ * scratch: fp32 [n, janus_logmel_frames_alloc(), n_mels]; maxbuf: int32 [n].
+ * mel_bf16_out (or NULL): bf16 [n, 3002, n_mels] time-major with zero rows 0 and 3001 (the encoder's
+ * conv padding); mel_f32_out (or NULL): fp32 [n, n_mels, 3000] (the reference's layout). */
+int32_t janus_logmel_frames_alloc(void);
+int32_t janus_logmel_f32(const float* pcm, const int64_t* offsets, const int64_t* lengths, int32_t n,
+                         int32_t decim, int32_t n_mels, const int32_t* mel_start, const int32_t* mel_len,
+                         const float* mel_w, int32_t mel_max_len, float* scratch, int32_t* maxbuf,
+                         void* mel_bf16_out, float* mel_f32_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K2: Whisper encoder (replaces CTranslate2 Whisper.encode reached from transcriber.py:53-57)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t n_mels, n_ctx, d, n_heads, n_layers;   /* n_ctx = 1500; input has 2*n_ctx frames */
+} janus_whisper_dims_t;
+
+typedef struct {          /* device pointers; matrices bf16 row-major [out, in], vectors fp32 */
+  const float* ln1_w; const float* ln1_b;
+  const void* w_qkv;  const float* b_qkv;    /* [3d, d]; the key third of b_qkv is zero (Whisper has no key bias) */
+  const void* w_o;    const float* b_o;
+  const float* ln2_w; const float* ln2_b;
+  const void* w_fc1;  const float* b_fc1;    /* [4d, d] */
+  const void* w_fc2;  const float* b_fc2;    /* [d, 4d] */
+} janus_enc_layer_t;
+
+typedef struct {
+  const void* conv1_w; const float* conv1_b;  /* bf16 [d, 3*n_mels], tap-major: [d][k][c] */
+  const void* conv2_w; const float* conv2_b;  /* bf16 [d, 3*d],      tap-major */
+  const float* pos;                            /* fp32 [n_ctx, d] sinusoids */
+  const float* ln_post_w; const float* ln_post_b;
+  const janus_enc_layer_t* layers;             /* HOST array, n_layers entries */
+} janus_encoder_weights_t;
+
+int64_t janus_whisper_encode_workspace_bytes(const janus_whisper_dims_t* dims, int32_t batch);
+/* mel_pad: bf16 [batch, 2*n_ctx+2, n_mels] (janus_logmel_f32's bf16 output); enc_out: bf16 [batch, n_ctx, d]. */
+int32_t janus_whisper_encode_bf16(const janus_whisper_dims_t* dims, const janus_encoder_weights_t* weights,
+                                  const void* mel_pad, int32_t batch, void* enc_out, void* workspace,
+                                  int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

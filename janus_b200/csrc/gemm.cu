@@ -15,7 +15,7 @@
 //               smem stages and publishes finished accumulators
 //   warps 2-9   epilogue: tcgen05.ld (32 lanes x 32 columns) -> bias / GELU / positional / residual
 //               -> bf16 stores; overlaps the next tile's mainloop through the second TMEM buffer.
-#include "tc_common.cuh"
+#include "kernels.cuh"
 
 namespace janus {
 
@@ -23,27 +23,6 @@ constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
 constexpr int GEMM_EPI_WARPS = 8;                       // 2 per TMEM lane quarter (column halves)
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
-
-enum GemmAct { ACT_NONE = 0, ACT_GELU = 1 };
-enum GemmStore { STORE_ROWMAJOR = 0, STORE_CROSS_KV = 1 };
-
-struct GemmParams {
-  int M_per_batch, n_batch, N, K;
-  int m_tiles_per_batch, n_tiles, total_tiles, k_tiles;
-  __nv_bfloat16* out;
-  long long ldc, out_batch_stride;
-  int out_row_offset;
-  const float* bias;                  // [N] or null
-  const __nv_bfloat16* residual;      // indexed like out, or null
-  const float* pos;                   // [M_per_batch, N] added after the activation, or null
-  int act;
-  int store_mode;
-  // STORE_CROSS_KV: N = n_layer * 2 * d; columns [l][k|v][h][64]. K goes to kT[l][b][h][64][kv_ld]
-  // (keys contiguous), V to v[l][b][h][t][64].
-  __nv_bfloat16* kv_k;
-  __nv_bfloat16* kv_v;
-  int kv_d, kv_heads, kv_ld;
-};
 
 template <int BN>
 struct GemmSmem {
