@@ -151,6 +151,61 @@ int32_t janus_whisper_encode_bf16(const janus_whisper_dims_t* dims, const janus_
                                   const void* mel_pad, int32_t batch, void* enc_out, void* workspace,
                                   int64_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * K3: Whisper decoder, greedy / temperature 0 (replaces CTranslate2 Whisper.generate + the
+ * faster-whisper logit rules executed while transcriber.py:59-64 iterates `segments`)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {          /* device pointers; matrices bf16 row-major [out, in], vectors fp32 */
+  const float* ln1_w; const float* ln1_b;
+  const void* w_qkv;  const float* b_qkv;    /* self-attention [3d, d]; key bias third is zero */
+  const void* w_o;    const float* b_o;
+  const float* lnc_w; const float* lnc_b;
+  const void* w_cq;   const float* b_cq;     /* cross-attention query / output projections */
+  const void* w_co;   const float* b_co;
+  const float* ln2_w; const float* ln2_b;
+  const void* w_fc1;  const float* b_fc1;
+  const void* w_fc2;  const float* b_fc2;
+} janus_dec_layer_t;
+
+typedef struct {
+  const void* tok_emb;                 /* bf16 [n_vocab_pad, d], rows >= n_vocab are zero (tied output head) */
+  const float* pos;                    /* fp32 [n_text_ctx, d] learned positions */
+  const float* ln_w; const float* ln_b;
+  const void* w_ckv; const float* b_ckv; /* all layers' cross K/V projections stacked: bf16 [L*2*d, d] as
+                                            [l][k|v][d]; fp32 bias with zeros in the key parts */
+  const uint8_t* suppress_mask;        /* [n_vocab] 1 = never emit (non-speech set + specials) */
+  const janus_dec_layer_t* layers;     /* HOST array, n_layers entries */
+  int32_t n_vocab, n_vocab_pad, n_text_ctx, kv_ld;   /* kv_ld = padded key count of the transposed cross-K cache */
+  int32_t eot, blank, timestamp_begin, max_initial_timestamp_index;
+} janus_decoder_weights_t;
+
+typedef struct {
+  int32_t batch, max_len, n_prompt;    /* max_len = n_prompt + max_new_tokens */
+  int32_t* tokens;                     /* [batch, max_len]; the sot prompt is pre-filled by the caller */
+  const int32_t* forced;               /* [batch, max_len] teacher forcing (-1 = free) or NULL */
+  int32_t* choice;                     /* [batch, max_len] argmax under the rules (diagnostic) or NULL */
+  float* logprob;                      /* [batch, max_len] log-prob of the rule-filtered argmax */
+  float* sum_logprob;                  /* [batch] */
+  int32_t* pos;                        /* device scalar: index of the token the next step consumes */
+  uint8_t* done;                       /* [batch] */
+  int32_t* n_done;                     /* device scalar */
+  void* self_k; void* self_v;          /* bf16 [L, batch, H, n_text_ctx, 64] */
+  const void* cross_k;                 /* bf16 [L, batch, H, 64, kv_ld]  (keys contiguous) */
+  const void* cross_v;                 /* bf16 [L, batch, H, n_ctx, 64] */
+  void* x; void* xn; void* qkv; void* att; void* q; void* ff;  /* bf16 [batch, d|d|3d|d|d|4d] */
+  float* logits;                       /* fp32 [batch, n_vocab_pad] */
+} janus_decode_state_t;
+
+/* Cross-attention K/V of all decoder layers for a batch of encoder outputs (one tcgen05 GEMM whose
+ * epilogue writes the two cache layouts directly). dims->n_layers/d/n_heads describe the DECODER. */
+int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,
+                                    const void* enc_out, int32_t batch, void* cross_k, void* cross_v, void* stream);
+/* One decode step for every stream of the batch: consumes tokens[:, *pos], emits tokens[:, *pos+1],
+ * then *pos += 1. Nothing in it depends on host-side scalars, so it can be captured once in a CUDA
+ * graph and replayed. */
+int32_t janus_whisper_decode_step(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,
+                                  const janus_decode_state_t* state, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

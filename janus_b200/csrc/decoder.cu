@@ -1,0 +1,410 @@
+// K3: Whisper KV-cache decoder (greedy, temperature 0) for a batch of independent windows.
+//
+// Replaces CTranslate2 `Whisper.generate` + faster-whisper's decode-time logit rules, which the
+// reference runs lazily while iterating `segments` (/root/reference/backend/services/transcriber.py:
+// 53-64, beam_size=1): token + learned positional embedding, n_layers x [LN -> causal self-attention
+// over the KV cache, LN -> cross-attention over the 1500 encoder states, LN -> MLP], LN, logits =
+// x E^T, SuppressBlank / SuppressTokens / ApplyTimestampRules, log-softmax, argmax.
+//
+// The step is memory-bound. Per stream and step it must read the cross K/V of every layer
+// (2 * L * 1500 * d bf16 = 55 MB for Whisper-small), so the cross-attention kernel owns the layout:
+//   cross K is stored TRANSPOSED  kT[l][b][h][64][1536]  -> scores: lanes <-> keys, 16-byte loads of 8
+//                                                            consecutive keys per dim, no shuffles
+//   cross V is stored row-major   v [l][b][h][1500][64]  -> PV: 8 lanes cover one 128-byte row
+// Both are written directly in those layouts by the tcgen05 GEMM epilogue (STORE_CROSS_KV).
+// The skinny (M = batch) linear layers reuse the tcgen05 GEMM with 64-wide N tiles so that every
+// weight byte is streamed exactly once per step by many CTAs; logits are produced in fp32 and the
+// rule filter + log-softmax + argmax run in one pass of one CTA per stream.
+// All per-step scalars (position, done flags) live in device memory so the whole step is one
+// CUDA graph that the host replays.
+#include "kernels.cuh"
+
+namespace janus {
+
+constexpr int DH = 64;
+
+// ------------------------------------------------------------------------------------------
+// embedding
+// ------------------------------------------------------------------------------------------
+__global__ void dec_embed_kernel(const int32_t* __restrict__ tokens, int max_len, const int32_t* __restrict__ pos_p,
+                                 const __nv_bfloat16* __restrict__ emb, const float* __restrict__ pos_emb, int d,
+                                 __nv_bfloat16* __restrict__ x) {
+  const int b = blockIdx.x;
+  const int pos = *pos_p;
+  const int tok = tokens[(long long)b * max_len + pos];
+  const __nv_bfloat16* e = emb + (long long)tok * d;
+  const float* pe = pos_emb + (long long)pos * d;
+  for (int i = threadIdx.x; i < d; i += blockDim.x)
+    x[(long long)b * d + i] = __float2bfloat16_rn(__bfloat162float(e[i]) + pe[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// causal self-attention over the KV cache: one warp per (head, stream)
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32)
+dec_self_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ kc,
+                     __nv_bfloat16* __restrict__ vc, const int32_t* __restrict__ pos_p, int d, int n_ctx,
+                     __nv_bfloat16* __restrict__ out) {
+  __shared__ float ps[512];
+  __shared__ float qs[DH];
+  const int h = blockIdx.x, b = blockIdx.y, H = gridDim.x, lane = threadIdx.x;
+  const int pos = *pos_p;
+  const __nv_bfloat16* row = qkv + (long long)b * 3 * d + h * DH;
+  __nv_bfloat16* K = kc + ((long long)b * H + h) * n_ctx * DH;
+  __nv_bfloat16* V = vc + ((long long)b * H + h) * n_ctx * DH;
+  // append this step's k, v
+  reinterpret_cast<__nv_bfloat162*>(K + (long long)pos * DH)[lane] = reinterpret_cast<const __nv_bfloat162*>(row + d)[lane];
+  reinterpret_cast<__nv_bfloat162*>(V + (long long)pos * DH)[lane] = reinterpret_cast<const __nv_bfloat162*>(row + 2 * d)[lane];
+  {
+    const float2 qq = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(row)[lane]);
+    qs[2 * lane] = qq.x * 0.125f;
+    qs[2 * lane + 1] = qq.y * 0.125f;
+  }
+  __syncwarp();
+  float mx = -INFINITY;
+  for (int j = lane; j <= pos; j += 32) {
+    const uint4* kr = reinterpret_cast<const uint4*>(K + (long long)j * DH);
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const uint4 u = kr[c];
+      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(hh[e]);
+        s = fmaf(f.x, qs[c * 8 + 2 * e], s);
+        s = fmaf(f.y, qs[c * 8 + 2 * e + 1], s);
+      }
+    }
+    ps[j] = s;
+    mx = fmaxf(mx, s);
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int j = lane; j <= pos; j += 32) {
+    const float p = __expf(ps[j] - mx);
+    ps[j] = p;
+    sum += p;
+  }
+  sum = warp_sum(sum);
+  __syncwarp();
+  float o0 = 0.f, o1 = 0.f;
+  for (int j = 0; j <= pos; ++j) {
+    const float2 f = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(V + (long long)j * DH)[lane]);
+    const float p = ps[j];
+    o0 = fmaf(p, f.x, o0);
+    o1 = fmaf(p, f.y, o1);
+  }
+  const float inv = 1.f / sum;
+  reinterpret_cast<__nv_bfloat162*>(out + (long long)b * d + h * DH)[lane] = __floats2bfloat162_rn(o0 * inv, o1 * inv);
+}
+
+// ------------------------------------------------------------------------------------------
+// cross-attention over the encoder states: one CTA per (head, stream); HBM-bound
+// ------------------------------------------------------------------------------------------
+constexpr int XA_THREADS = 192;  // 192 * 8 keys = 1536 >= 1500
+
+__global__ void __launch_bounds__(XA_THREADS)
+dec_cross_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ kT,
+                      const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, __nv_bfloat16* __restrict__ out) {
+  __shared__ float qs[DH];
+  __shared__ __align__(16) float ps[XA_THREADS * 8];
+  __shared__ float red[XA_THREADS / 8][DH];
+  __shared__ float wred[2][XA_THREADS / 32];
+  const int h = blockIdx.x, b = blockIdx.y, H = gridDim.x, tid = threadIdx.x;
+  const long long bh = (long long)b * H + h;
+  if (tid < DH) qs[tid] = __bfloat162float(q[(long long)b * d + h * DH + tid]) * (0.125f * 1.4426950408889634f);
+  __syncthreads();
+  // ---- scores for keys 8*tid .. 8*tid+7
+  const int key0 = tid * 8;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  if (key0 < kv_ld) {
+    const uint4* kp = reinterpret_cast<const uint4*>(kT + bh * DH * kv_ld + key0);
+    const int stride = kv_ld >> 3;  // uint4 per dim row
+#pragma unroll 16
+    for (int dim = 0; dim < DH; ++dim) {
+      const uint4 u = __ldg(kp + (long long)dim * stride);
+      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+      const float qd = qs[dim];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(hh[e]);
+        acc[2 * e] = fmaf(f.x, qd, acc[2 * e]);
+        acc[2 * e + 1] = fmaf(f.y, qd, acc[2 * e + 1]);
+      }
+    }
+  }
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    acc[i] = (key0 + i < T) ? acc[i] : -INFINITY;  // select, not multiply: the pad keys are uninitialised
+    mx = fmaxf(mx, acc[i]);
+  }
+  mx = warp_max(mx);
+  if ((tid & 31) == 0) wred[0][tid >> 5] = mx;
+  __syncthreads();
+  mx = wred[0][0];
+#pragma unroll
+  for (int w = 1; w < XA_THREADS / 32; ++w) mx = fmaxf(mx, wred[0][w]);
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float p = exp2f(acc[i] - mx);
+    ps[key0 + i] = p;
+    sum += p;
+  }
+  sum = warp_sum(sum);
+  if ((tid & 31) == 0) wred[1][tid >> 5] = sum;
+  __syncthreads();
+  sum = 0.f;
+#pragma unroll
+  for (int w = 0; w < XA_THREADS / 32; ++w) sum += wred[1][w];
+  // ---- PV: 8 lanes per 128-byte V row, 24 rows per pass
+  const int c = tid & 7, rg = tid >> 3;
+  float o[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] = 0.f;
+  const uint4* vp = reinterpret_cast<const uint4*>(v + bh * (long long)T * DH) + c;
+#pragma unroll 8
+  for (int j = rg; j < T; j += XA_THREADS / 8) {
+    const uint4 u = __ldg(vp + (long long)j * 8);
+    const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+    const float p = ps[j];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(hh[e]);
+      o[2 * e] = fmaf(p, f.x, o[2 * e]);
+      o[2 * e + 1] = fmaf(p, f.y, o[2 * e + 1]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[rg][c * 8 + i] = o[i];
+  __syncthreads();
+  if (tid < DH) {
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < XA_THREADS / 8; ++r) t += red[r][tid];
+    out[(long long)b * d + h * DH + tid] = __float2bfloat16_rn(t / sum);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// logit rules + log-softmax + argmax: one CTA per stream, one pass over the fp32 logits
+// ------------------------------------------------------------------------------------------
+struct PickParams {
+  const float* logits;  // [B, n_vocab_pad]
+  const uint8_t* suppress;
+  int32_t* tokens;
+  const int32_t* forced;
+  int32_t* choice;
+  float* logprob;
+  float* sum_logprob;
+  int32_t* pos;
+  uint8_t* done;
+  int32_t* n_done;
+  int n_vocab, n_vocab_pad, max_len, n_prompt, eot, blank, ts_begin, max_initial_ts;
+};
+
+struct Stat {  // running (max, argmax, sum exp(x - max))
+  float m;
+  int idx;
+  float s;
+};
+__device__ __forceinline__ void stat_add(Stat& a, float x, int i) {
+  if (x > a.m) {
+    a.s = a.s * __expf(a.m - x) + 1.f;
+    a.m = x;
+    a.idx = i;
+  } else {
+    a.s += __expf(x - a.m);
+  }
+}
+__device__ __forceinline__ void stat_merge(Stat& a, const Stat& o) {
+  if (o.m == -INFINITY) return;
+  if (a.m == -INFINITY) { a = o; return; }
+  if (o.m > a.m || (o.m == a.m && o.idx < a.idx)) {
+    a.s = a.s * __expf(a.m - o.m) + o.s;
+    a.m = o.m;
+    a.idx = o.idx;
+  } else {
+    a.s += o.s * __expf(o.m - a.m);
+  }
+}
+__device__ __forceinline__ Stat stat_shfl(const Stat& a, int o) {
+  Stat r;
+  r.m = __shfl_xor_sync(FULL_MASK, a.m, o);
+  r.idx = __shfl_xor_sync(FULL_MASK, a.idx, o);
+  r.s = __shfl_xor_sync(FULL_MASK, a.s, o);
+  return r;
+}
+
+constexpr int PICK_THREADS = 512;
+
+__global__ void __launch_bounds__(PICK_THREADS) dec_pick_kernel(const PickParams p) {
+  __shared__ Stat sh[2][PICK_THREADS / 32];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int pos = *p.pos;        // index of the token just consumed; we choose token pos+1
+  const int nxt = pos + 1;
+  if (nxt >= p.max_len) return;
+  int32_t* toks = p.tokens + (long long)b * p.max_len;
+  if (nxt < p.n_prompt) return;  // still feeding the prompt
+  const int n_gen = nxt - p.n_prompt;
+  const int tb = p.ts_begin;
+  // rule state from the already emitted tokens (ApplyTimestampRules)
+  const int last = n_gen >= 1 ? toks[nxt - 1] : -1;
+  const int penult = n_gen >= 2 ? toks[nxt - 2] : -1;
+  const bool last_ts = n_gen >= 1 && last >= tb;
+  const bool penult_ts = n_gen < 2 || penult >= tb;
+  int ts_floor = tb;  // timestamps below this are forbidden
+  {
+    // the last timestamp emitted so far (they never decrease, so it is the max)
+    int last_stamp = -1;
+    for (int i = p.n_prompt; i < nxt; ++i) {
+      const int t = toks[i];
+      if (t >= tb) last_stamp = t;
+    }
+    if (last_stamp >= 0) ts_floor = (last_ts && !penult_ts) ? last_stamp : last_stamp + 1;
+  }
+  const float* lg = p.logits + (long long)b * p.n_vocab_pad;
+  Stat text = {-INFINITY, 0x7fffffff, 0.f}, ts = {-INFINITY, 0x7fffffff, 0.f};
+  for (int i = tid; i < p.n_vocab; i += PICK_THREADS) {
+    bool ok = !p.suppress[i];
+    if (n_gen == 0) {
+      ok = ok && i != p.blank && i != p.eot;                            // SuppressBlank
+      ok = ok && i >= tb && i <= tb + p.max_initial_ts;                 // first token: timestamp <= 1.0 s
+    }
+    if (last_ts) ok = ok && (penult_ts ? i < tb : i >= p.eot);          // pairs of timestamps
+    if (i >= tb) ok = ok && i >= ts_floor;                              // monotone timestamps
+    if (!ok) continue;
+    const float x = lg[i];
+    if (i < tb) stat_add(text, x, i); else stat_add(ts, x, i);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    stat_merge(text, stat_shfl(text, o));
+    stat_merge(ts, stat_shfl(ts, o));
+  }
+  if ((tid & 31) == 0) { sh[0][tid >> 5] = text; sh[1][tid >> 5] = ts; }
+  __syncthreads();
+  if (tid == 0) {
+    text = sh[0][0]; ts = sh[1][0];
+    for (int w = 1; w < PICK_THREADS / 32; ++w) { stat_merge(text, sh[0][w]); stat_merge(ts, sh[1][w]); }
+    const float lse_ts = ts.m == -INFINITY ? -INFINITY : ts.m + logf(ts.s);
+    int tok;
+    float lp;
+    if (lse_ts > text.m) {  // timestamps carry more mass than any text token: sample a timestamp
+      tok = ts.idx;
+      lp = ts.m - lse_ts;
+    } else {
+      Stat all = text;
+      stat_merge(all, ts);
+      tok = all.idx;
+      lp = -logf(all.s);
+    }
+    const bool was_done = p.done[b] != 0;
+    if (p.choice) p.choice[(long long)b * p.max_len + nxt] = tok;
+    int emit = tok;
+    if (p.forced) {
+      const int f = p.forced[(long long)b * p.max_len + nxt];
+      if (f >= 0) emit = f;
+    }
+    if (was_done) { emit = p.eot; lp = 0.f; }
+    toks[nxt] = emit;
+    p.logprob[(long long)b * p.max_len + nxt] = lp;
+    if (!was_done) {
+      p.sum_logprob[b] += lp;
+      if (emit == p.eot) { p.done[b] = 1; atomicAdd(p.n_done, 1); }
+    }
+  }
+}
+
+__global__ void dec_advance_kernel(int32_t* pos) { *pos += 1; }
+
+}  // namespace janus
+
+using namespace janus;
+
+static GemmParams skinny(void* out, int B, int N, int K, const float* bias, const void* res, int act, int store) {
+  GemmParams q = {};
+  q.M_per_batch = B; q.n_batch = 1; q.N = N; q.K = K;
+  q.out = static_cast<__nv_bfloat16*>(out); q.ldc = N; q.out_batch_stride = (long long)B * N;
+  q.bias = bias; q.residual = static_cast<const __nv_bfloat16*>(res); q.act = act; q.store_mode = store;
+  q.bn_max = 64;
+  return q;
+}
+
+extern "C" int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                               const void* enc_out, int32_t batch, void* cross_k, void* cross_v,
+                                               void* stream) {
+  JANUS_CHECK_ARG(c && w && enc_out && cross_k && cross_v && batch > 0, "cross_kv: bad argument");
+  const int T = c->n_ctx, d = c->d;
+  GemmParams p = {};
+  p.M_per_batch = T; p.n_batch = batch; p.N = c->n_layers * 2 * d; p.K = d;
+  p.bias = w->b_ckv; p.store_mode = STORE_CROSS_KV;
+  p.kv_k = static_cast<__nv_bfloat16*>(cross_k); p.kv_v = static_cast<__nv_bfloat16*>(cross_v);
+  p.kv_d = d; p.kv_heads = c->n_heads; p.kv_ld = w->kv_ld;
+  p.ldc = 0; p.out_batch_stride = 0;
+  return gemm_bf16(static_cast<const __nv_bfloat16*>(enc_out), d, (long long)T * d,
+                   static_cast<const __nv_bfloat16*>(w->w_ckv), d, p, (cudaStream_t)stream);
+}
+
+extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                             const janus_decode_state_t* s, void* stream_) {
+  JANUS_CHECK_ARG(c && w && s, "decode_step: null pointer");
+  JANUS_CHECK_ARG(c->d == c->n_heads * 64, "decode_step: head_dim must be 64");
+  JANUS_CHECK_ARG(c->n_ctx <= XA_THREADS * 8 && w->kv_ld % 8 == 0 && w->kv_ld >= c->n_ctx && w->kv_ld <= XA_THREADS * 8,
+                  "decode_step: n_ctx=%d / kv_ld=%d unsupported", c->n_ctx, w->kv_ld);
+  JANUS_CHECK_ARG(w->n_text_ctx <= 512, "decode_step: n_text_ctx must be <= 512");
+  cudaStream_t st = (cudaStream_t)stream_;
+  const int B = s->batch, d = c->d, H = c->n_heads, T = c->n_ctx;
+  __nv_bfloat16* x = static_cast<__nv_bfloat16*>(s->x);
+  __nv_bfloat16* xn = static_cast<__nv_bfloat16*>(s->xn);
+  __nv_bfloat16* qkv = static_cast<__nv_bfloat16*>(s->qkv);
+  __nv_bfloat16* att = static_cast<__nv_bfloat16*>(s->att);
+  __nv_bfloat16* q = static_cast<__nv_bfloat16*>(s->q);
+  __nv_bfloat16* ff = static_cast<__nv_bfloat16*>(s->ff);
+  int rc;
+  dec_embed_kernel<<<B, 128, 0, st>>>(s->tokens, s->max_len, s->pos, static_cast<const __nv_bfloat16*>(w->tok_emb),
+                                      w->pos, d, x);
+  JANUS_LAUNCH_CHECK("dec_embed_kernel");
+  const long long self_stride = (long long)B * H * w->n_text_ctx * DH;
+  const long long ck_stride = (long long)B * H * DH * w->kv_ld;
+  const long long cv_stride = (long long)B * H * T * DH;
+  for (int l = 0; l < c->n_layers; ++l) {
+    const janus_dec_layer_t& L = w->layers[l];
+    auto W = [](const void* p) { return static_cast<const __nv_bfloat16*>(p); };
+    if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st))) return rc;
+    if ((rc = gemm_bf16(xn, d, (long long)B * d, W(L.w_qkv), d, skinny(qkv, B, 3 * d, d, L.b_qkv, nullptr, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    dec_self_attn_kernel<<<dim3(H, B), 32, 0, st>>>(qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
+                                                    static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d,
+                                                    w->n_text_ctx, att);
+    JANUS_LAUNCH_CHECK("dec_self_attn_kernel");
+    if ((rc = gemm_bf16(att, d, (long long)B * d, W(L.w_o), d, skinny(x, B, d, d, L.b_o, x, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st))) return rc;
+    if ((rc = gemm_bf16(xn, d, (long long)B * d, W(L.w_cq), d, skinny(q, B, d, d, L.b_cq, nullptr, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    dec_cross_attn_kernel<<<dim3(H, B), XA_THREADS, 0, st>>>(
+        q, static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
+        static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att);
+    JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
+    if ((rc = gemm_bf16(att, d, (long long)B * d, W(L.w_co), d, skinny(x, B, d, d, L.b_co, x, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st))) return rc;
+    if ((rc = gemm_bf16(xn, d, (long long)B * d, W(L.w_fc1), d, skinny(ff, B, 4 * d, d, L.b_fc1, nullptr, ACT_GELU, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = gemm_bf16(ff, 4 * d, (long long)B * 4 * d, W(L.w_fc2), 4 * d, skinny(x, B, d, 4 * d, L.b_fc2, x, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+  }
+  if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st))) return rc;
+  if ((rc = gemm_bf16(xn, d, (long long)B * d, static_cast<const __nv_bfloat16*>(w->tok_emb), d,
+                      skinny(s->logits, B, w->n_vocab_pad, d, nullptr, nullptr, ACT_NONE, STORE_F32), st))) return rc;
+  PickParams pp;
+  pp.logits = s->logits; pp.suppress = w->suppress_mask; pp.tokens = s->tokens; pp.forced = s->forced;
+  pp.choice = s->choice; pp.logprob = s->logprob; pp.sum_logprob = s->sum_logprob; pp.pos = s->pos;
+  pp.done = s->done; pp.n_done = s->n_done; pp.n_vocab = w->n_vocab; pp.n_vocab_pad = w->n_vocab_pad;
+  pp.max_len = s->max_len; pp.n_prompt = s->n_prompt; pp.eot = w->eot; pp.blank = w->blank;
+  pp.ts_begin = w->timestamp_begin; pp.max_initial_ts = w->max_initial_timestamp_index;
+  dec_pick_kernel<<<B, PICK_THREADS, 0, st>>>(pp);
+  JANUS_LAUNCH_CHECK("dec_pick_kernel");
+  dec_advance_kernel<<<1, 1, 0, st>>>(s->pos);
+  JANUS_LAUNCH_CHECK("dec_advance_kernel");
+  return JANUS_OK;
+}

@@ -182,7 +182,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
               }
             }
           }
-          if (p.store_mode == STORE_ROWMAJOR) {
+          if (p.store_mode == STORE_F32) {
+            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + row_off + n0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) op[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          } else if (p.store_mode == STORE_ROWMAJOR) {
             uint4* op = reinterpret_cast<uint4*>(p.out + row_off + n0);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
@@ -317,7 +321,8 @@ int gemm_bf16(const __nv_bfloat16* A, long long lda, long long a_batch_stride, c
                   "gemm: operands must be 16 B aligned");
   p.m_tiles_per_batch = (p.M_per_batch + GEMM_BM - 1) / GEMM_BM;
   p.k_tiles = (p.K + GEMM_BK - 1) / GEMM_BK;
-  const int BN = (p.N % 256 == 0) ? 256 : (p.N % 128 == 0 ? 128 : 64);
+  int BN = (p.N % 256 == 0) ? 256 : (p.N % 128 == 0 ? 128 : 64);
+  if (p.bn_max > 0 && BN > p.bn_max) BN = p.bn_max >= 128 ? 128 : 64;
   CUtensorMap ta, tb;
   {
     const uint64_t dims[3] = {(uint64_t)p.K, (uint64_t)p.M_per_batch, (uint64_t)p.n_batch};

@@ -5,7 +5,7 @@
 namespace janus {
 
 enum GemmAct { ACT_NONE = 0, ACT_GELU = 1 };
-enum GemmStore { STORE_ROWMAJOR = 0, STORE_CROSS_KV = 1 };
+enum GemmStore { STORE_ROWMAJOR = 0, STORE_CROSS_KV = 1, STORE_F32 = 2 };
 
 struct GemmParams {
   int M_per_batch, n_batch, N, K;
@@ -23,6 +23,7 @@ struct GemmParams {
   __nv_bfloat16* kv_k;
   __nv_bfloat16* kv_v;
   int kv_d, kv_heads, kv_ld;
+  int bn_max;  // 0 = auto; otherwise cap the N tile (skinny-M decode GEMMs want many small tiles)
 };
 
 int gemm_bf16(const __nv_bfloat16* A, long long lda, long long a_batch_stride, const __nv_bfloat16* W,

@@ -39,6 +39,7 @@ class WhisperEngine:
         self._keep: list[torch.Tensor] = []   # owns every device tensor referenced by the C structs
         self.frontend = LogMelFrontend(dims.n_mels, self.device)
         self._pack_encoder(weights)
+        self._pack_decoder(weights)
         self._enc_ws: torch.Tensor | None = None
 
     # ---- packing ----------------------------------------------------------------------------
@@ -103,3 +104,164 @@ class WhisperEngine:
         out = torch.zeros((B, T + 2, M), dtype=torch.bfloat16, device=self.device)
         out[:, 1:T + 1] = mel.to(self.device).permute(0, 2, 1).to(torch.bfloat16)
         return out
+
+
+# ==============================================================================================
+# decoder (K3)
+# ==============================================================================================
+class DecLayerStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("ln1_w", "ln1_b", "w_qkv", "b_qkv", "w_o", "b_o", "lnc_w", "lnc_b",
+                                          "w_cq", "b_cq", "w_co", "b_co", "ln2_w", "ln2_b", "w_fc1", "b_fc1",
+                                          "w_fc2", "b_fc2")]
+
+
+class DecWeightsStruct(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("tok_emb", "pos", "ln_w", "ln_b", "w_ckv", "b_ckv", "suppress_mask")] + \
+               [("layers", C.POINTER(DecLayerStruct))] + \
+               [(n, C.c_int32) for n in ("n_vocab", "n_vocab_pad", "n_text_ctx", "kv_ld", "eot", "blank",
+                                         "timestamp_begin", "max_initial_timestamp_index")]
+
+
+class DecodeStateStruct(C.Structure):
+    _fields_ = [("batch", C.c_int32), ("max_len", C.c_int32), ("n_prompt", C.c_int32)] + \
+               [(n, C.c_void_p) for n in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done",
+                                          "n_done", "self_k", "self_v", "cross_k", "cross_v", "x", "xn", "qkv",
+                                          "att", "q", "ff", "logits")]
+
+
+def _pack_decoder(self, W) -> None:
+    d, spec = self.dims, self.spec
+    n, L = d.n_text_state, d.n_text_layer
+    self.c_dec_dims = DimsStruct(d.n_mels, d.n_audio_ctx, n, d.n_text_head, L)
+    self.dec_layers = (DecLayerStruct * L)()
+    ckv_w, ckv_b = [], []
+    for i in range(L):
+        p = f"dec.l{i}"
+        S = self.dec_layers[i]
+        wqkv = torch.cat([W[p + ".attn.q.w"], W[p + ".attn.k.w"], W[p + ".attn.v.w"]], 0)
+        bqkv = torch.cat([W[p + ".attn.q.b"], torch.zeros(n), W[p + ".attn.v.b"]], 0)
+        S.ln1_w, S.ln1_b = self._f32(W[p + ".attn_ln.w"]).data_ptr(), self._f32(W[p + ".attn_ln.b"]).data_ptr()
+        S.w_qkv, S.b_qkv = self._bf16(wqkv).data_ptr(), self._f32(bqkv).data_ptr()
+        S.w_o, S.b_o = self._bf16(W[p + ".attn.o.w"]).data_ptr(), self._f32(W[p + ".attn.o.b"]).data_ptr()
+        S.lnc_w, S.lnc_b = self._f32(W[p + ".cross_ln.w"]).data_ptr(), self._f32(W[p + ".cross_ln.b"]).data_ptr()
+        S.w_cq, S.b_cq = self._bf16(W[p + ".cross.q.w"]).data_ptr(), self._f32(W[p + ".cross.q.b"]).data_ptr()
+        S.w_co, S.b_co = self._bf16(W[p + ".cross.o.w"]).data_ptr(), self._f32(W[p + ".cross.o.b"]).data_ptr()
+        S.ln2_w, S.ln2_b = self._f32(W[p + ".mlp_ln.w"]).data_ptr(), self._f32(W[p + ".mlp_ln.b"]).data_ptr()
+        S.w_fc1, S.b_fc1 = self._bf16(W[p + ".mlp.fc1.w"]).data_ptr(), self._f32(W[p + ".mlp.fc1.b"]).data_ptr()
+        S.w_fc2, S.b_fc2 = self._bf16(W[p + ".mlp.fc2.w"]).data_ptr(), self._f32(W[p + ".mlp.fc2.b"]).data_ptr()
+        ckv_w += [W[p + ".cross.k.w"], W[p + ".cross.v.w"]]
+        ckv_b += [torch.zeros(n), W[p + ".cross.v.b"]]
+    dw = DecWeightsStruct()
+    vpad = -(-d.n_vocab // 64) * 64
+    emb = torch.zeros(vpad, n)
+    emb[:d.n_vocab] = W["dec.tok_emb"]
+    dw.tok_emb = self._bf16(emb).data_ptr()
+    dw.pos = self._f32(W["dec.pos"]).data_ptr()
+    dw.ln_w, dw.ln_b = self._f32(W["dec.ln.w"]).data_ptr(), self._f32(W["dec.ln.b"]).data_ptr()
+    dw.w_ckv = self._bf16(torch.cat(ckv_w, 0)).data_ptr()
+    dw.b_ckv = self._f32(torch.cat(ckv_b, 0)).data_ptr()
+    mask = torch.zeros(d.n_vocab, dtype=torch.uint8)
+    mask[list(spec.suppress_ids)] = 1
+    dw.suppress_mask = self._dev(mask, torch.uint8).data_ptr()
+    dw.layers = C.cast(self.dec_layers, C.POINTER(DecLayerStruct))
+    dw.n_vocab, dw.n_vocab_pad, dw.n_text_ctx = d.n_vocab, vpad, d.n_text_ctx
+    dw.kv_ld = -(-d.n_audio_ctx // 64) * 64
+    dw.eot, dw.blank, dw.timestamp_begin = spec.eot, spec.blank, spec.timestamp_begin
+    dw.max_initial_timestamp_index = spec.max_initial_timestamp_index
+    self.dec_weights = dw
+    self.n_vocab_pad, self.kv_ld = vpad, int(dw.kv_ld)
+
+
+WhisperEngine._pack_decoder = _pack_decoder
+
+
+class DecodeSession:
+    """Greedy decode of a fixed-size batch: owns the KV caches and the captured CUDA graph of one step."""
+
+    def __init__(self, engine: WhisperEngine, batch: int, max_new_tokens: int, use_graph: bool = True) -> None:
+        if not hasattr(engine, "dec_weights"):
+            raise RuntimeError("engine was built without decoder weights")
+        self.eng, self.B = engine, batch
+        d, spec, dev = engine.dims, engine.spec, engine.device
+        self.n_prompt = len(spec.sot_sequence)
+        self.max_new = min(max_new_tokens, spec.max_length - self.n_prompt)
+        self.max_len = self.n_prompt + self.max_new
+        n, L, H = d.n_text_state, d.n_text_layer, d.n_text_head
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        i32 = dict(dtype=torch.int32, device=dev)
+        B = batch
+        self.tokens = torch.zeros((B, self.max_len), **i32)
+        self.forced = torch.full((B, self.max_len), -1, **i32)
+        self.choice = torch.zeros((B, self.max_len), **i32)
+        self.logprob = torch.zeros((B, self.max_len), dtype=torch.float32, device=dev)
+        self.sum_logprob = torch.zeros(B, dtype=torch.float32, device=dev)
+        self.pos = torch.zeros(1, **i32)
+        self.done = torch.zeros(B, dtype=torch.uint8, device=dev)
+        self.n_done = torch.zeros(1, **i32)
+        self.self_k = torch.zeros((L, B, H, d.n_text_ctx, 64), **bf)
+        self.self_v = torch.zeros((L, B, H, d.n_text_ctx, 64), **bf)
+        self.cross_k = torch.zeros((L, B, H, 64, engine.kv_ld), **bf)
+        self.cross_v = torch.zeros((L, B, H, d.n_audio_ctx, 64), **bf)
+        self.x, self.xn = torch.zeros((B, n), **bf), torch.zeros((B, n), **bf)
+        self.qkv, self.att = torch.zeros((B, 3 * n), **bf), torch.zeros((B, n), **bf)
+        self.q, self.ff = torch.zeros((B, n), **bf), torch.zeros((B, 4 * n), **bf)
+        self.logits = torch.zeros((B, engine.n_vocab_pad), dtype=torch.float32, device=dev)
+        self.prompt = torch.tensor(list(spec.sot_sequence), **i32)
+        s = DecodeStateStruct()
+        s.batch, s.max_len, s.n_prompt = B, self.max_len, self.n_prompt
+        for name in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done", "n_done", "self_k",
+                     "self_v", "cross_k", "cross_v", "x", "xn", "qkv", "att", "q", "ff", "logits"):
+            setattr(s, name, getattr(self, name).data_ptr())
+        self.state = s
+        self.use_graph = use_graph
+        self.graph: torch.cuda.CUDAGraph | None = None
+        self.n_steps = self.n_prompt + self.max_new - 1
+        self.kernels_per_step = 3 + 11 * L + 2 + 1  # embed, final LN, logits, pick, advance + 11 per layer
+
+    def _step(self) -> None:
+        e = self.eng
+        _abi.call("janus_whisper_decode_step", C.byref(e.c_dec_dims), C.byref(e.dec_weights), C.byref(self.state),
+                  torch.cuda.current_stream(e.device).cuda_stream)
+
+    def reset(self, forced: torch.Tensor | None = None) -> None:
+        self.tokens.zero_()
+        self.tokens[:, :self.n_prompt] = self.prompt
+        self.forced.fill_(-1)
+        if forced is not None:  # [B, max_new] tokens to teacher-force after the prompt
+            k = min(forced.shape[1], self.max_new)
+            self.forced[:, self.n_prompt:self.n_prompt + k] = forced[:, :k].to(self.forced)
+        self.pos.zero_()
+        self.done.zero_()
+        self.n_done.zero_()
+        self.sum_logprob.zero_()
+        self.logprob.zero_()
+
+    def cross_kv(self, enc_out: torch.Tensor) -> None:
+        e = self.eng
+        assert enc_out.shape[0] == self.B and enc_out.dtype == torch.bfloat16 and enc_out.is_contiguous()
+        _abi.call("janus_whisper_cross_kv_bf16", C.byref(e.c_dec_dims), C.byref(e.dec_weights), enc_out.data_ptr(),
+                  self.B, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
+                  torch.cuda.current_stream(e.device).cuda_stream)
+
+    def _ensure_graph(self) -> None:
+        if not self.use_graph or self.graph is not None:
+            return
+        self.reset()
+        self._step()  # eager warm-up: sets kernel attributes outside capture
+        torch.cuda.current_stream(self.eng.device).synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._step()
+        self.graph = g
+
+    def decode(self, enc_out: torch.Tensor, forced: torch.Tensor | None = None, n_steps: int | None = None):
+        """Returns (tokens [B, max_new] int32 device, sum_logprob [B]). Does not synchronise."""
+        self._ensure_graph()
+        self.cross_kv(enc_out)
+        self.reset(forced)
+        for _ in range(self.n_steps if n_steps is None else n_steps):
+            if self.graph is not None:
+                self.graph.replay()
+            else:
+                self._step()
+        return self.tokens[:, self.n_prompt:], self.sum_logprob

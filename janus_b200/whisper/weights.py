@@ -27,11 +27,24 @@ def sinusoids(length: int, channels: int, max_timescale: float = 10000.0) -> tor
     return torch.cat([torch.sin(t), torch.cos(t)], dim=1)
 
 
-def init_random_weights(dims: WhisperDims, seed: int = 0, gain: float = 0.7,
-                        emb_row_spread: float = 1.0, bf16_exact: bool = True) -> dict[str, torch.Tensor]:
+PROFILES = {
+    # near-flat logits, varied tokens: exercises every code path; greedy margins are small, so token
+    # parity is asserted only where the fp32 margin exceeds the stated bf16 logit tolerance
+    "diverse": dict(gain=1.0, emb_row_spread=0.3, qk_gain=3.0, pos_std=1.0),
+    # heavy-tailed tied embedding -> peaked distribution (like a trained model): top-1 margins are far
+    # above bf16 noise, so free-running greedy tokens must be bit-exact
+    "confident": dict(gain=0.7, emb_row_spread=0.3, qk_gain=3.0, pos_std=0.3),
+}
+
+
+def init_random_weights(dims: WhisperDims, seed: int = 0, gain: float = 0.7, emb_row_spread: float = 0.3,
+                        qk_gain: float = 1.0, pos_std: float = 0.3, bf16_exact: bool = True,
+                        profile: str | None = None) -> dict[str, torch.Tensor]:
     """Seeded random weights. `emb_row_spread` is the log-normal sigma of the per-token norm of the
     tied token embedding: it makes the logit distribution heavy-tailed (like a trained model's peaked
     distribution) so greedy top-1 margins sit far above bf16 noise."""
+    if profile is not None:
+        return init_random_weights(dims, seed, bf16_exact=bf16_exact, **PROFILES[profile])
     g = torch.Generator().manual_seed(seed)
     W: dict[str, torch.Tensor] = {}
 
@@ -50,6 +63,8 @@ def init_random_weights(dims: WhisperDims, seed: int = 0, gain: float = 0.7,
     def attn(prefix, n):
         linear(prefix + ".q", n, n)
         linear(prefix + ".k", n, n, bias=False)
+        W[prefix + ".q.w"] *= qk_gain
+        W[prefix + ".k.w"] *= qk_gain
         linear(prefix + ".v", n, n)
         linear(prefix + ".o", n, n)
 
@@ -71,7 +86,7 @@ def init_random_weights(dims: WhisperDims, seed: int = 0, gain: float = 0.7,
     t = dims.n_text_state
     row = torch.exp(randn(dims.n_vocab, std=emb_row_spread))
     W["dec.tok_emb"] = randn(dims.n_vocab, t, std=1.0 / math.sqrt(t)) * row[:, None]
-    W["dec.pos"] = randn(dims.n_text_ctx, t, std=0.3)
+    W["dec.pos"] = randn(dims.n_text_ctx, t, std=pos_std)
     for i in range(dims.n_text_layer):
         p = f"dec.l{i}"
         ln(p + ".attn_ln", t)

@@ -1,0 +1,102 @@
+"""K3 parity on a real B200: KV-cache greedy decoder (through the C ABI) vs the fp32 CPU oracle.
+
+Stated tolerances (bf16 kernels vs fp32 oracle; logits have std ~1-3):
+  * teacher-forced final-step logits: |err| <= 0.06 + 0.02*|ref|
+  * the rule-filtered argmax equals the oracle's token at EVERY step whose fp32 top-1/top-2 margin
+    exceeds MARGIN_TOL = 0.15 (2.5x the logit tolerance); the log-prob of the emitted token is within 0.08
+  * "confident" weights (peaked distribution, margins >> bf16 noise): free-running greedy tokens are
+    bit-exact, end to end from audio.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+MARGIN_TOL = 0.15
+
+
+def _setup(profile, seed, n_clips=3, layers=2, d=128, heads=2):
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.engine import WhisperEngine
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = test_dims(d=d, heads=heads, layers=layers)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=seed, profile=profile)
+    clips = make_clips(n_clips, 30.0, 16000, seed=77).numpy()
+    mel = torch.stack([torch.from_numpy(log_mel_window(c, dims.n_mels)) for c in clips])
+    enc_ref = R.encode(W, dims, mel)
+    eng = WhisperEngine(dims, W, torch.device("cuda", 0))
+    return dims, spec, W, clips, mel, enc_ref, eng, R
+
+
+def test_teacher_forced_vs_oracle():
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, clips, mel, enc_ref, eng, R = _setup("diverse", 3)
+    n_new = 40
+    ref_tok, ref_lp, margins = R.greedy_decode(W, dims, spec, enc_ref, n_new, return_margins=True)
+    # feed the ORACLE's encoder states (rounded to bf16) so this test isolates the decoder
+    enc_bf16 = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    for use_graph in (False, True):
+        ses = DecodeSession(eng, batch=len(clips), max_new_tokens=n_new, use_graph=use_graph)
+        toks, sum_lp = ses.decode(enc_bf16, forced=ref_tok.cuda())
+        torch.cuda.synchronize()
+        assert torch.equal(toks.cpu().long(), ref_tok)  # forced
+        choice = ses.choice[:, ses.n_prompt:].cpu().long()
+        safe = margins > MARGIN_TOL
+        assert bool((choice[safe] == ref_tok[safe]).all()), "argmax differs where the fp32 margin is large"
+        print(f"graph={use_graph}: argmax agreement {float((choice == ref_tok).float().mean()):.3f} overall, "
+              f"{int(safe.sum())}/{safe.numel()} steps above margin tol")
+        # final-step logits vs oracle
+        st = R.DecoderState(W, dims, enc_ref)
+        full = torch.cat([torch.tensor([list(spec.sot_sequence)] * len(clips)), ref_tok[:, :-1]], 1)
+        ref_logits = st.step(full)[:, -1]
+        got = ses.logits[:, :dims.n_vocab].cpu()
+        err = (got - ref_logits).abs()
+        print(f"logit err max {err.max():.4f} mean {err.mean():.5f} (ref std {ref_logits.std():.3f})")
+        assert bool((err <= 0.06 + 0.02 * ref_logits.abs()).all())
+
+
+def test_greedy_bit_exact_confident_end_to_end():
+    """audio -> K1 log-mel -> K2 encoder -> cross-KV -> K3 greedy == oracle pipeline, token for token."""
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, clips, mel, enc_ref, eng, R = _setup("confident", 3)
+    n_new = 32
+    ref_tok, ref_lp, margins = R.greedy_decode(W, dims, spec, enc_ref, n_new, return_margins=True)
+    dev = eng.device
+    lens = torch.tensor([len(c) for c in clips], dtype=torch.int64)
+    offs = torch.cumsum(lens, 0) - lens
+    pcm = torch.from_numpy(np.concatenate(clips)).to(dev)
+    mel_pad, _ = eng.frontend(pcm, offs.to(dev), lens.to(dev))
+    enc = eng.encode(mel_pad)
+    ses = DecodeSession(eng, batch=len(clips), max_new_tokens=n_new)
+    toks, sum_lp = ses.decode(enc)
+    torch.cuda.synchronize()
+    print("min oracle margin", float(margins[margins < 1e30].min()), "tokens", toks[0, :8].tolist())
+    assert torch.equal(toks.cpu().long(), ref_tok)
+    assert torch.allclose(sum_lp.cpu(), ref_lp, atol=0.3, rtol=0.02)
+    # second decode on the same session (graph replay, state reset) is deterministic
+    toks2, _ = ses.decode(enc)
+    assert torch.equal(toks2, toks)
+
+
+def test_cross_kv_layouts():
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, clips, mel, enc_ref, eng, R = _setup("diverse", 5, n_clips=2)
+    ses = DecodeSession(eng, batch=2, max_new_tokens=4, use_graph=False)
+    enc_bf16 = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    ses.cross_kv(enc_bf16)
+    torch.cuda.synchronize()
+    x = enc_bf16.float().cpu()
+    for l in range(dims.n_text_layer):
+        k = x @ W[f"dec.l{l}.cross.k.w"].T
+        v = x @ W[f"dec.l{l}.cross.v.w"].T + W[f"dec.l{l}.cross.v.b"]
+        H = dims.n_text_head
+        k = k.view(2, 1500, H, 64).permute(0, 2, 3, 1)       # [B, H, 64, T]
+        v = v.view(2, 1500, H, 64).permute(0, 2, 1, 3)       # [B, H, T, 64]
+        gk = ses.cross_k[l, :, :, :, :1500].float().cpu()
+        gv = ses.cross_v[l].float().cpu()
+        assert bool(((gk - k).abs() <= 2e-2 * k.abs().clamp(min=1)).all())
+        assert bool(((gv - v).abs() <= 2e-2 * v.abs().clamp(min=1)).all())
