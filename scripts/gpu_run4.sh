@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_decoder.py -x -q -s 2>&1 | tail -40
+timeout 900 python -m pytest tests/test_gpu_decoder.py -q -s > gpurun_out/dec_test.log 2>&1
+grep -E "graph=|logit err|min oracle|passed|failed|Error|error" gpurun_out/dec_test.log | head -30
