@@ -70,7 +70,7 @@ def cpu_prosody_throughput(n_clips: int, seconds: float, sr: int, procs: int, se
     return n_clips * seconds / wall, wall, lags / hops
 
 
-def run_reference(args) -> None:
+def run_reference_prosody(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -161,7 +161,7 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------
-def run_gpu(args) -> None:
+def run_gpu_prosody(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -325,18 +325,26 @@ def main() -> None:
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="janus_b200", choices=["janus_b200", "reference"])
-    ap.add_argument("--streams", type=int, default=4096, help="streams per GPU")
+    ap.add_argument("--workload", default="stt_prosody", choices=["stt_prosody", "prosody"],
+                    help="stt_prosody = the headline metric (Whisper STT + prosody -> packets); "
+                         "prosody = BASELINE configs[1] alone")
+    ap.add_argument("--model", default="small")
+    ap.add_argument("--batch", type=int, default=64, help="30 s windows per GPU per step (stt_prosody)")
+    ap.add_argument("--max-new-tokens", type=int, default=128)
+    ap.add_argument("--streams", type=int, default=4096, help="streams per GPU (prosody workload)")
     ap.add_argument("--clip-seconds", type=float, default=30.0)
     ap.add_argument("--sample-rate", type=int, default=16000)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-clips", type=int, default=0)
     ap.add_argument("--ref-clips", type=int, default=0)
+    ap.add_argument("--ref-windows", type=int, default=2, help="windows per CPU reference step (stt_prosody)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
+    if args.workload == "prosody":
+        (run_reference_prosody if args.impl == "reference" else run_gpu_prosody)(args)
     else:
-        run_gpu(args)
+        from bench_stt import run_gpu_stt, run_reference_stt
+        (run_reference_stt if args.impl == "reference" else run_gpu_stt)(args)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,259 @@
+"""Headline workload of bench.py: Whisper STT (log-mel -> encoder -> greedy decoder) + YIN/RMS prosody
+-> MessagePack packets, on a batch of 30 s synthetic 16 kHz windows per GPU (BASELINE configs[2] plus
+the prosody leg of the metric)."""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import numpy as np
+
+from bench import METRIC, ROOT, UNIT, ClockSampler, cpu_prosody_throughput
+
+
+def stt_config(args, batch: int) -> dict:
+    return {
+        "workload": f"Whisper-{args.model} (random-init, bf16) log-mel + encoder + greedy decode of "
+                    f"{args.max_new_tokens} tokens per 30 s window, plus aubio-equivalent YIN pitch / RMS prosody "
+                    "on the same windows -> MessagePack packets (BASELINE configs[2] + prosody)",
+        "windows_per_gpu": batch, "clip_seconds": args.clip_seconds, "sample_rate": args.sample_rate,
+        "max_new_tokens": args.max_new_tokens,
+        "parallelism": f"dp{args.gpus} over independent windows, no collective",
+        "l2": "per-step working set (cross-KV 3.5 GB + activations) is far larger than the 126 MB L2",
+    }
+
+
+# ------------------------------------------------------------------------------------------
+# CPU: the oracle restatement of the reference path, all host threads
+# ------------------------------------------------------------------------------------------
+def cpu_stt_prosody(args, n_windows: int, cores: int):
+    """One bounded sample: n_windows windows through log-mel (numpy) -> Whisper fp32 (torch, all
+    threads) greedy decode -> YIN oracle (one process per core) -> packets. Returns (audio-s/s, detail)."""
+    import torch
+    from janus_b200.protocol import JanusMode, JanusPacket
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import PRESETS, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = PRESETS[args.model]
+    spec = tokenizer_spec(dims)
+    torch.set_num_threads(cores)
+    W = init_random_weights(dims, seed=0, profile="confident")
+    clips = make_clips(n_windows, args.clip_seconds, args.sample_rate, seed=1234).numpy()
+    t0 = time.perf_counter()
+    mel = torch.stack([torch.from_numpy(log_mel_window(c, dims.n_mels)) for c in clips])
+    t_mel = time.perf_counter() - t0
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        enc = R.encode(W, dims, mel)
+        t_enc = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        toks, _ = R.greedy_decode(W, dims, spec, enc, args.max_new_tokens, stop_at_eot=False)
+        t_dec = time.perf_counter() - t0
+    pros_rate, t_pros, lph = cpu_prosody_throughput(n_windows, args.clip_seconds, args.sample_rate, min(cores, n_windows))
+    t0 = time.perf_counter()
+    for i in range(n_windows):
+        JanusPacket("synthetic", JanusMode.SEMANTIC_VOICE, {'energy': 'Normal', 'pitch': 'Normal'}, None, 0.0).serialize()
+    t_pkt = time.perf_counter() - t0
+    total = t_mel + t_enc + t_dec + t_pros + t_pkt
+    detail = {"logmel_s": t_mel, "encoder_s": t_enc, "decoder_s": t_dec, "prosody_s": t_pros, "total_s": total}
+    return n_windows * args.clip_seconds / total, detail
+
+
+def run_reference_stt(args) -> None:
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = os.cpu_count() or 1
+    n = args.ref_windows
+    for _ in range(min(args.warmup, 1)):
+        cpu_stt_prosody(args, 1, cores)
+    vals, t_all = [], time.perf_counter()
+    detail = {}
+    for _ in range(args.steps):
+        v, detail = cpu_stt_prosody(args, n, cores)
+        vals.append(v)
+    value = float(np.mean(vals))
+    sample = (f"{n} windows x {args.clip_seconds:g} s per step: numpy log-mel + fp32 PyTorch Whisper-{args.model} oracle "
+              f"({cores} threads) greedy {args.max_new_tokens} tokens + YIN oracle + packets; faster-whisper / "
+              "CTranslate2 / aubio are not installable on this box (no network)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * (time.perf_counter() - t_all) / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": stt_config(args, n),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, **detail},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# GPU
+# ------------------------------------------------------------------------------------------
+def run_gpu_stt(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cores = os.cpu_count() or 1
+    B, seconds, sr = args.batch, args.clip_seconds, args.sample_rate
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, detail = cpu_stt_prosody(args, 1, cores)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": f"1 window x {seconds:g} s: numpy log-mel + fp32 PyTorch Whisper-{args.model} oracle "
+                                  f"({cores} threads) greedy {args.max_new_tokens} tokens + YIN oracle + packet", **detail}
+
+    import torch
+    import torch.distributed as dist
+    from janus_b200 import _abi
+    from janus_b200.pipeline import SemanticEncoder
+    from janus_b200.synth import make_clips
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
+                          prosody_sample_rate=sr, input_sample_rate=sr)
+    N = int(round(seconds * sr))
+    x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)
+    lengths = tuple([N] * B)
+
+    def step_device():
+        return enc.encode_device(x, lengths)
+
+    W_ = max(args.warmup, 3)
+    for _ in range(W_):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- stage breakdown (device time, one step, events between stages)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+    plan, offs, lens, pros_out = enc._plan(lengths)
+    ev[0].record()
+    enc.prosody.run(x, plan, out=pros_out)
+    ev[1].record()
+    enc.whisper.frontend(x, offs, lens, decim=enc.decim, scratch=enc.mel_scratch, out_bf16=enc.mel_pad)
+    ev[2].record()
+    enc.whisper.encode(enc.mel_pad, out=enc.enc_out)
+    ev[3].record()
+    enc.session.cross_kv(enc.enc_out)
+    ev[4].record()
+    enc.session.reset()
+    for _ in range(enc.session.n_steps):
+        enc.session.graph.replay()
+    ev[5].record()
+    torch.cuda.synchronize()
+    stages = {k: ev[i].elapsed_time(ev[i + 1]) for i, k in
+              enumerate(["prosody_ms", "logmel_ms", "encoder_ms", "cross_kv_ms", "decoder_ms"])}
+
+    # ---- dominant kernel alone: decode-time cross-attention (HBM-bound), per launch over all layers
+    ses = enc.session
+    d = enc.dims
+    stream = torch.cuda.current_stream(dev)
+    k_ms = []
+    for rep in range(3):
+        a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for l in range(d.n_text_layer):
+            _abi.call("janus_dec_cross_attn_bf16", ses.q.data_ptr(), ses.cross_k[l].data_ptr(), ses.cross_v[l].data_ptr(),
+                      ses.att.data_ptr(), B, d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld, stream.cuda_stream)
+        b_.record(stream)
+        torch.cuda.synchronize()
+        if rep:
+            k_ms.append(a.elapsed_time(b_) / d.n_text_layer)
+    xattn_ms = float(np.mean(k_ms))
+
+    # ---- end to end: pinned host PCM -> H2D -> all kernels -> D2H tokens/tags -> detokenise -> packets
+    host = torch.empty(x.numel(), dtype=torch.float32, pin_memory=True)
+    host.copy_(x)
+    xd = torch.empty_like(x)
+    tok_host = torch.empty((B, ses.max_new), dtype=torch.int32, pin_memory=True)
+    tag_host = torch.empty((B, 2), dtype=torch.uint8, pin_memory=True)
+    n_pkts = 0
+
+    def step_e2e():
+        nonlocal n_pkts
+        xd.copy_(host, non_blocking=True)
+        r = enc.encode_device(xd, lengths)
+        tok_host.copy_(r.tokens, non_blocking=True)
+        tag_host.copy_(r.tags, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        texts, pk = enc.to_packets(tok_host.numpy(), tag_host.numpy(), timestamps=[0.0] * B)
+        n_pkts = sum(p is not None for p in pk)
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+
+    t = torch.tensor([ms_total, e2e_ms, xattn_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms, xattn_ms = (float(v) for v in t.cpu())
+
+    if rank == 0:
+        audio_s_step = world * B * seconds
+        value = audio_s_step * args.steps / (ms_total / 1e3)
+        e2e_value = audio_s_step * e2e_steps / (e2e_ms / 1e3)
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            hbm_peak, tf_peak, peak_src = float(peaks["hbm_gbs"]), float(peaks["bf16_tflops_sustained"]), \
+                "measured (MEASURED_PEAKS.json)"
+        except Exception:  # noqa: BLE001
+            hbm_peak, tf_peak, peak_src = 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
+        H, T, kv_ld = d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld
+        # algorithmic bytes of one cross-attention launch: K and V of every (stream, head) once, q in, out out
+        alg_bytes = B * H * (2 * T * 64 * 2) + 2 * B * d.n_text_state * 2
+        achieved = alg_bytes / (xattn_ms / 1e3) / 1e9
+        # encoder tensor-pipe figure for context (SURVEY 8d FLOP count)
+        dd, L, Ta = d.n_audio_state, d.n_audio_layer, d.n_audio_ctx
+        enc_flops = B * (L * (8 * dd * dd * Ta + 4 * Ta * Ta * dd + 16 * dd * dd * Ta)
+                         + 2 * (2 * Ta) * dd * 3 * d.n_mels + 2 * Ta * dd * 3 * dd)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": W_,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic", "config": stt_config(args, B), "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(x.numel() * 4 * world),
+                    "d2h_bytes_per_step": int((tok_host.numel() * 4 + 2 * B) * world), "steps": e2e_steps,
+                    "packets_per_step": n_pkts * world},
+            "gpu_launches": enc.kernels_per_step() * args.steps,
+            "stages_ms": stages,
+            "roofline": {"kernel": "dec_cross_attn_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "kernel_ms": xattn_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                         "launches_per_step": d.n_text_layer * ses.n_steps,
+                         "encoder_tensor": {"tflops": enc_flops / (stages["encoder_ms"] / 1e3) / 1e12,
+                                            "peak": tf_peak, "frac": enc_flops / (stages["encoder_ms"] / 1e3) / 1e12 / tf_peak,
+                                            "algorithmic_flops": enc_flops}},
+        }
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()

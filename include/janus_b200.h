@@ -196,6 +196,11 @@ typedef struct {
   float* logits;                       /* fp32 [batch, n_vocab_pad] */
 } janus_decode_state_t;
 
+/* One layer of decode-time cross-attention (the HBM-bound kernel of the step), exposed for parity tests
+ * and roofline timing: q bf16 [batch, 64*n_heads]; cross_k bf16 [batch, n_heads, 64, kv_ld];
+ * cross_v bf16 [batch, n_heads, n_ctx, 64]; out bf16 [batch, 64*n_heads]. */
+int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
+                                  int32_t batch, int32_t n_heads, int32_t n_ctx, int32_t kv_ld, void* stream);
 /* Cross-attention K/V of all decoder layers for a batch of encoder outputs (one tcgen05 GEMM whose
  * epilogue writes the two cache layouts directly). dims->n_layers/d/n_heads describe the DECODER. */
 int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,

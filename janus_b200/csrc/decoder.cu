@@ -335,6 +335,19 @@ static GemmParams skinny(void* out, int B, int N, int K, const float* bias, cons
   return q;
 }
 
+extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
+                                             int32_t batch, int32_t n_heads, int32_t n_ctx, int32_t kv_ld,
+                                             void* stream) {
+  JANUS_CHECK_ARG(q && cross_k && cross_v && out && batch > 0 && n_heads > 0, "cross_attn: bad argument");
+  JANUS_CHECK_ARG(n_ctx <= XA_THREADS * 8 && kv_ld % 8 == 0 && kv_ld >= n_ctx && kv_ld <= XA_THREADS * 8,
+                  "cross_attn: n_ctx=%d / kv_ld=%d unsupported", n_ctx, kv_ld);
+  dec_cross_attn_kernel<<<dim3(n_heads, batch), XA_THREADS, 0, (cudaStream_t)stream>>>(
+      static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(cross_k),
+      static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, static_cast<__nv_bfloat16*>(out));
+  JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
+  return JANUS_OK;
+}
+
 extern "C" int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
                                                const void* enc_out, int32_t batch, void* cross_k, void* cross_v,
                                                void* stream) {
