@@ -196,6 +196,11 @@ typedef struct {
   float* logits;                       /* fp32 [batch, n_vocab_pad] */
 } janus_decode_state_t;
 
+/* Skinny linear layer of the decode step: out[r, n] = act(sum_k A[r,k] W[n,k] + bias[n]) (+ residual[r,n]),
+ * rows <= 256, A bf16 [rows, K] (leading dim lda), W bf16 [N, K], out bf16 or fp32 [rows, N]. */
+int32_t janus_dec_linear_bf16(const void* A, int32_t lda, const void* W, const float* bias, const void* residual,
+                              void* out, int32_t rows, int32_t N, int32_t K, int32_t act, int32_t out_f32,
+                              void* stream);
 /* One layer of decode-time cross-attention (the HBM-bound kernel of the step), exposed for parity tests
  * and roofline timing: q bf16 [batch, 64*n_heads]; cross_k bf16 [batch, n_heads, 64, kv_ld];
  * cross_v bf16 [batch, n_heads, n_ctx, 64]; out bf16 [batch, 64*n_heads]. */

@@ -12,8 +12,8 @@
 //                                                            consecutive keys per dim, no shuffles
 //   cross V is stored row-major   v [l][b][h][1500][64]  -> PV: 8 lanes cover one 128-byte row
 // Both are written directly in those layouts by the tcgen05 GEMM epilogue (STORE_CROSS_KV).
-// The skinny (M = batch) linear layers reuse the tcgen05 GEMM with 64-wide N tiles so that every
-// weight byte is streamed exactly once per step by many CTAs; logits are produced in fp32 and the
+// The skinny (M = batch) linear layers use a dedicated register-streaming kernel (dec_linear.cu): every
+// weight byte is read exactly once per step by hundreds of warps; logits are produced in fp32 and the
 // rule filter + log-softmax + argmax run in one pass of one CTA per stream.
 // All per-step scalars (position, done flags) live in device memory so the whole step is one
 // CUDA graph that the host replays.
@@ -269,17 +269,29 @@ __global__ void __launch_bounds__(PICK_THREADS) dec_pick_kernel(const PickParams
   }
   const float* lg = p.logits + (long long)b * p.n_vocab_pad;
   Stat text = {-INFINITY, 0x7fffffff, 0.f}, ts = {-INFINITY, 0x7fffffff, 0.f};
-  for (int i = tid; i < p.n_vocab; i += PICK_THREADS) {
-    bool ok = !p.suppress[i];
-    if (n_gen == 0) {
-      ok = ok && i != p.blank && i != p.eot;                            // SuppressBlank
-      ok = ok && i >= tb && i <= tb + p.max_initial_ts;                 // first token: timestamp <= 1.0 s
+  // 4 tokens per thread per iteration: one 16-byte logit load + one 4-byte mask load
+  const int first_lo = tb, first_hi = tb + p.max_initial_ts;
+  for (int i0 = tid * 4; i0 < p.n_vocab; i0 += PICK_THREADS * 4) {
+    const float4 x4 = *reinterpret_cast<const float4*>(lg + i0);   // rows are padded to a multiple of 64
+    uint32_t sup4;
+    if (i0 + 3 < p.n_vocab) {
+      sup4 = *reinterpret_cast<const uint32_t*>(p.suppress + i0);
+    } else {
+      sup4 = 0x01010101u;
+      for (int e = 0; e < 4 && i0 + e < p.n_vocab; ++e)
+        sup4 = (sup4 & ~(0xffu << (8 * e))) | ((uint32_t)p.suppress[i0 + e] << (8 * e));
     }
-    if (last_ts) ok = ok && (penult_ts ? i < tb : i >= p.eot);          // pairs of timestamps
-    if (i >= tb) ok = ok && i >= ts_floor;                              // monotone timestamps
-    if (!ok) continue;
-    const float x = lg[i];
-    if (i < tb) stat_add(text, x, i); else stat_add(ts, x, i);
+    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = i0 + e;
+      bool ok = ((sup4 >> (8 * e)) & 0xffu) == 0;
+      if (n_gen == 0) ok = ok && i != p.blank && i != p.eot && i >= first_lo && i <= first_hi;  // SuppressBlank + first timestamp <= 1.0 s
+      if (last_ts) ok = ok && (penult_ts ? i < tb : i >= p.eot);          // timestamps come in pairs
+      if (i >= tb) ok = ok && i >= ts_floor;                              // monotone timestamps
+      if (!ok) continue;
+      if (i < tb) stat_add(text, xs[e], i); else stat_add(ts, xs[e], i);
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -325,15 +337,6 @@ __global__ void dec_advance_kernel(int32_t* pos) { *pos += 1; }
 }  // namespace janus
 
 using namespace janus;
-
-static GemmParams skinny(void* out, int B, int N, int K, const float* bias, const void* res, int act, int store) {
-  GemmParams q = {};
-  q.M_per_batch = B; q.n_batch = 1; q.N = N; q.K = K;
-  q.out = static_cast<__nv_bfloat16*>(out); q.ldc = N; q.out_batch_stride = (long long)B * N;
-  q.bias = bias; q.residual = static_cast<const __nv_bfloat16*>(res); q.act = act; q.store_mode = store;
-  q.bn_max = 64;
-  return q;
-}
 
 extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
                                              int32_t batch, int32_t n_heads, int32_t n_ctx, int32_t kv_ld,
@@ -389,26 +392,26 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
     const janus_dec_layer_t& L = w->layers[l];
     auto W = [](const void* p) { return static_cast<const __nv_bfloat16*>(p); };
     if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = gemm_bf16(xn, d, (long long)B * d, W(L.w_qkv), d, skinny(qkv, B, 3 * d, d, L.b_qkv, nullptr, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = dec_linear(xn, d, W(L.w_qkv), L.b_qkv, nullptr, qkv, B, 3 * d, d, ACT_NONE, 0, st))) return rc;
     dec_self_attn_kernel<<<dim3(H, B), 32, 0, st>>>(qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
                                                     static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d,
                                                     w->n_text_ctx, att);
     JANUS_LAUNCH_CHECK("dec_self_attn_kernel");
-    if ((rc = gemm_bf16(att, d, (long long)B * d, W(L.w_o), d, skinny(x, B, d, d, L.b_o, x, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = dec_linear(att, d, W(L.w_o), L.b_o, x, x, B, d, d, ACT_NONE, 0, st))) return rc;
     if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = gemm_bf16(xn, d, (long long)B * d, W(L.w_cq), d, skinny(q, B, d, d, L.b_cq, nullptr, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = dec_linear(xn, d, W(L.w_cq), L.b_cq, nullptr, q, B, d, d, ACT_NONE, 0, st))) return rc;
     dec_cross_attn_kernel<<<dim3(H, B), XA_THREADS, 0, st>>>(
         q, static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
         static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att);
     JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
-    if ((rc = gemm_bf16(att, d, (long long)B * d, W(L.w_co), d, skinny(x, B, d, d, L.b_co, x, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = dec_linear(att, d, W(L.w_co), L.b_co, x, x, B, d, d, ACT_NONE, 0, st))) return rc;
     if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = gemm_bf16(xn, d, (long long)B * d, W(L.w_fc1), d, skinny(ff, B, 4 * d, d, L.b_fc1, nullptr, ACT_GELU, STORE_ROWMAJOR), st))) return rc;
-    if ((rc = gemm_bf16(ff, 4 * d, (long long)B * 4 * d, W(L.w_fc2), 4 * d, skinny(x, B, d, 4 * d, L.b_fc2, x, ACT_NONE, STORE_ROWMAJOR), st))) return rc;
+    if ((rc = dec_linear(xn, d, W(L.w_fc1), L.b_fc1, nullptr, ff, B, 4 * d, d, ACT_GELU, 0, st))) return rc;
+    if ((rc = dec_linear(ff, 4 * d, W(L.w_fc2), L.b_fc2, x, x, B, d, 4 * d, ACT_NONE, 0, st))) return rc;
   }
   if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st))) return rc;
-  if ((rc = gemm_bf16(xn, d, (long long)B * d, static_cast<const __nv_bfloat16*>(w->tok_emb), d,
-                      skinny(s->logits, B, w->n_vocab_pad, d, nullptr, nullptr, ACT_NONE, STORE_F32), st))) return rc;
+  if ((rc = dec_linear(xn, d, static_cast<const __nv_bfloat16*>(w->tok_emb), nullptr, nullptr, s->logits, B,
+                       w->n_vocab_pad, d, ACT_NONE, 1, st))) return rc;
   PickParams pp;
   pp.logits = s->logits; pp.suppress = w->suppress_mask; pp.tokens = s->tokens; pp.forced = s->forced;
   pp.choice = s->choice; pp.logprob = s->logprob; pp.sum_logprob = s->sum_logprob; pp.pos = s->pos;

@@ -32,5 +32,8 @@ int layernorm_bf16(const __nv_bfloat16* x, const float* w, const float* b, __nv_
                    long long ldx, long long ldy, cudaStream_t stream);
 int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int T, int n_heads, cudaStream_t stream);
 int num_sms();
+int dec_linear(const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, const float* bias,
+               const __nv_bfloat16* residual, void* out, int rows, int N, int K, int act, int out_f32,
+               cudaStream_t stream);
 
 }  // namespace janus

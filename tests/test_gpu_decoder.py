@@ -1,7 +1,8 @@
 """K3 parity on a real B200: KV-cache greedy decoder (through the C ABI) vs the fp32 CPU oracle.
 
 Stated tolerances (bf16 kernels vs fp32 oracle; logits have std ~1-3):
-  * teacher-forced final-step logits: |err| <= 0.08 + 0.04*|ref| everywhere, mean |err| <= 0.02
+  * teacher-forced final-step logits: |err_i| <= 0.02 + 0.1*||E_i|| (E_i = embedding row of token i; i.e. a
+    ~1% perturbation of the unit-variance final hidden state), mean |err| <= 0.02
   * the rule-filtered argmax equals the oracle's token at EVERY step whose fp32 top-1/top-2 margin
     exceeds MARGIN_TOL = 0.3; the log-prob of the emitted token is within 0.08
   * "confident" weights (peaked distribution, margins >> bf16 noise): free-running greedy tokens are
@@ -56,7 +57,8 @@ def test_teacher_forced_vs_oracle():
         got = ses.logits[:, :dims.n_vocab].cpu()
         err = (got - ref_logits).abs()
         print(f"logit err max {err.max():.4f} mean {err.mean():.5f} (ref std {ref_logits.std():.3f})")
-        ratio = (err / (0.08 + 0.04 * ref_logits.abs())).max()
+        row_norm = W["dec.tok_emb"].norm(dim=1)[None, :]   # logit_i = x . E_i, so its error scales with |E_i|
+        ratio = (err / (0.02 + 0.1 * row_norm)).max()
         print(f"logit tolerance ratio {ratio:.3f}")
         assert ratio <= 1.0 and err.mean() <= 0.02
 

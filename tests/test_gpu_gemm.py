@@ -83,3 +83,27 @@ def test_batched_overlapping_rows_conv_view():
     h = out[:, 1:T + 1].float().permute(0, 2, 1)
     ref2 = torch.nn.functional.gelu(torch.nn.functional.conv1d(h, w2.float(), bias, stride=2, padding=1))
     _check(out2, ref2.permute(0, 2, 1) + pos)
+
+
+@pytest.mark.parametrize("rows,N,K", [(64, 768, 768), (64, 2304, 768), (64, 768, 3072), (3, 128, 128), (100, 384, 1536),
+                                      (64, 51904, 768), (256, 1280, 1280)])
+def test_dec_linear(rows, N, K):
+    from janus_b200 import _abi
+    torch.manual_seed(rows + N + K)
+    A = torch.randn(rows, K, device="cuda").bfloat16()
+    W = (torch.randn(N, K, device="cuda") / K ** 0.5).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    res = torch.randn(rows, N, device="cuda").bfloat16()
+    st = torch.cuda.current_stream().cuda_stream
+    base = A.float() @ W.float().T + bias
+    out = torch.zeros(rows, N, device="cuda", dtype=torch.bfloat16)
+    _abi.call("janus_dec_linear_bf16", A.data_ptr(), K, W.data_ptr(), bias.data_ptr(), res.data_ptr(), out.data_ptr(),
+              rows, N, K, 0, 0, st)
+    _check(out, base + res.float())
+    _abi.call("janus_dec_linear_bf16", A.data_ptr(), K, W.data_ptr(), bias.data_ptr(), None, out.data_ptr(),
+              rows, N, K, 1, 0, st)
+    _check(out, torch.nn.functional.gelu(base))
+    out32 = torch.zeros(rows, N, device="cuda", dtype=torch.float32)
+    _abi.call("janus_dec_linear_bf16", A.data_ptr(), K, W.data_ptr(), None, None, out32.data_ptr(), rows, N, K, 0, 1, st)
+    torch.cuda.synchronize()
+    assert float((out32 - (base - bias)).abs().max()) <= 2e-3
