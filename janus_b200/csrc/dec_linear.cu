@@ -44,18 +44,31 @@ dec_linear_kernel(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloa
   for (int m = 0; m < MT; ++m) acc[m][0] = acc[m][1] = acc[m][2] = acc[m][3] = 0.f;
   const uint4* wp = reinterpret_cast<const uint4*>(W + (long long)(n0 + g) * K + 8 * t4);
   const bool col_ok = n0 + g < N;
-#pragma unroll 4
-  for (int kb = kb0; kb < kb1; ++kb) {
-    uint4 wv = make_uint4(0, 0, 0, 0);
-    if (col_ok) wv = __ldg(wp + kb * 4);  // 32 k = 64 B = 4 uint4 per row per k-block
+  // Issue a whole batch of weight loads before touching them: the op is one DRAM round trip, so
+  // what matters is how many bytes are in flight, not how fast they are consumed.
+  constexpr int PF = MT <= 4 ? 12 : (MT <= 8 ? 8 : 4);
+#pragma unroll 1
+  for (int kbase = kb0; kbase < kb1; kbase += PF) {
+    uint4 wv[PF];
 #pragma unroll
-    for (int m = 0; m < MT; ++m) {
-      const int r0 = 16 * m + g, r1 = r0 + 8;
-      uint4 a_lo = make_uint4(0, 0, 0, 0), a_hi = make_uint4(0, 0, 0, 0);
-      if (r0 < rows) a_lo = __ldg(reinterpret_cast<const uint4*>(A + (long long)r0 * lda + kb * 32 + 8 * t4));
-      if (r1 < rows) a_hi = __ldg(reinterpret_cast<const uint4*>(A + (long long)r1 * lda + kb * 32 + 8 * t4));
-      mma_bf16_16816(acc[m], a_lo.x, a_hi.x, a_lo.y, a_hi.y, wv.x, wv.y);
-      mma_bf16_16816(acc[m], a_lo.z, a_hi.z, a_lo.w, a_hi.w, wv.z, wv.w);
+    for (int i = 0; i < PF; ++i) {
+      wv[i] = make_uint4(0, 0, 0, 0);
+      if (col_ok && kbase + i < kb1) wv[i] = __ldg(wp + (kbase + i) * 4);  // 32 k = 64 B = 4 uint4 per row
+    }
+#pragma unroll
+    for (int i = 0; i < PF; ++i) {
+      const int kb = kbase + i;
+      if (kb < kb1) {
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+          const int r0 = 16 * m + g, r1 = r0 + 8;
+          uint4 a_lo = make_uint4(0, 0, 0, 0), a_hi = make_uint4(0, 0, 0, 0);
+          if (r0 < rows) a_lo = __ldg(reinterpret_cast<const uint4*>(A + (long long)r0 * lda + kb * 32 + 8 * t4));
+          if (r1 < rows) a_hi = __ldg(reinterpret_cast<const uint4*>(A + (long long)r1 * lda + kb * 32 + 8 * t4));
+          mma_bf16_16816(acc[m], a_lo.x, a_hi.x, a_lo.y, a_hi.y, wv[i].x, wv[i].y);
+          mma_bf16_16816(acc[m], a_lo.z, a_hi.z, a_lo.w, a_hi.w, wv[i].z, wv[i].w);
+        }
+      }
     }
   }
   if (kh == 1) {

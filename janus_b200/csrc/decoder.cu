@@ -338,6 +338,21 @@ __global__ void dec_advance_kernel(int32_t* pos) { *pos += 1; }
 
 using namespace janus;
 
+// Skinny linear dispatch. Up to 64 streams the register-streaming mma.sync kernel has the shorter
+// dependency chain for K <= 1024; for more streams (or long K / the vocabulary projection) the
+// tcgen05 GEMM with 64-wide N tiles fills its 128-row MMA tiles and wins.
+static int linear(const __nv_bfloat16* A, int K, const void* W, const float* bias, const __nv_bfloat16* residual,
+                  void* out, int rows, int N, int act, int out_f32, cudaStream_t st) {
+  if (rows <= 64 && K <= 1024 && N <= 8192)
+    return dec_linear(A, K, static_cast<const __nv_bfloat16*>(W), bias, residual, out, rows, N, K, act, out_f32, st);
+  GemmParams q = {};
+  q.M_per_batch = rows; q.n_batch = 1; q.N = N; q.K = K;
+  q.out = static_cast<__nv_bfloat16*>(out); q.ldc = N; q.out_batch_stride = (long long)rows * N;
+  q.bias = bias; q.residual = residual; q.act = act; q.store_mode = out_f32 ? STORE_F32 : STORE_ROWMAJOR;
+  q.bn_max = 64;
+  return gemm_bf16(A, K, (long long)rows * K, static_cast<const __nv_bfloat16*>(W), K, q, st);
+}
+
 extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
                                              int32_t batch, int32_t n_heads, int32_t n_ctx, int32_t kv_ld,
                                              void* stream) {
@@ -390,28 +405,26 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   const long long cv_stride = (long long)B * H * T * DH;
   for (int l = 0; l < c->n_layers; ++l) {
     const janus_dec_layer_t& L = w->layers[l];
-    auto W = [](const void* p) { return static_cast<const __nv_bfloat16*>(p); };
     if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = dec_linear(xn, d, W(L.w_qkv), L.b_qkv, nullptr, qkv, B, 3 * d, d, ACT_NONE, 0, st))) return rc;
+    if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st))) return rc;
     dec_self_attn_kernel<<<dim3(H, B), 32, 0, st>>>(qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
                                                     static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d,
                                                     w->n_text_ctx, att);
     JANUS_LAUNCH_CHECK("dec_self_attn_kernel");
-    if ((rc = dec_linear(att, d, W(L.w_o), L.b_o, x, x, B, d, d, ACT_NONE, 0, st))) return rc;
+    if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st))) return rc;
     if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = dec_linear(xn, d, W(L.w_cq), L.b_cq, nullptr, q, B, d, d, ACT_NONE, 0, st))) return rc;
+    if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st))) return rc;
     dec_cross_attn_kernel<<<dim3(H, B), XA_THREADS, 0, st>>>(
         q, static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
         static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att);
     JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
-    if ((rc = dec_linear(att, d, W(L.w_co), L.b_co, x, x, B, d, d, ACT_NONE, 0, st))) return rc;
+    if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st))) return rc;
     if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = dec_linear(xn, d, W(L.w_fc1), L.b_fc1, nullptr, ff, B, 4 * d, d, ACT_GELU, 0, st))) return rc;
-    if ((rc = dec_linear(ff, 4 * d, W(L.w_fc2), L.b_fc2, x, x, B, d, 4 * d, ACT_NONE, 0, st))) return rc;
+    if ((rc = linear(xn, d, L.w_fc1, L.b_fc1, nullptr, ff, B, 4 * d, ACT_GELU, 0, st))) return rc;
+    if ((rc = linear(ff, 4 * d, L.w_fc2, L.b_fc2, x, x, B, d, ACT_NONE, 0, st))) return rc;
   }
   if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st))) return rc;
-  if ((rc = dec_linear(xn, d, static_cast<const __nv_bfloat16*>(w->tok_emb), nullptr, nullptr, s->logits, B,
-                       w->n_vocab_pad, d, ACT_NONE, 1, st))) return rc;
+  if ((rc = linear(xn, d, w->tok_emb, nullptr, nullptr, s->logits, B, w->n_vocab_pad, ACT_NONE, 1, st))) return rc;
   PickParams pp;
   pp.logits = s->logits; pp.suppress = w->suppress_mask; pp.tokens = s->tokens; pp.forced = s->forced;
   pp.choice = s->choice; pp.logprob = s->logprob; pp.sum_logprob = s->sum_logprob; pp.pos = s->pos;

@@ -62,7 +62,7 @@ class SemanticEncoder:
 
     def __init__(self, model: str | WhisperDims = "small", batch: int = 64, max_new_tokens: int = 128,
                  device=None, seed: int = 0, weights: dict | None = None, weight_profile: str = "confident",
-                 prosody_sample_rate: int = 16000, input_sample_rate: int = 16000) -> None:
+                 prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, enc_chunk: int = 64) -> None:
         self.dims = PRESETS[model] if isinstance(model, str) else model
         self.spec = tokenizer_spec(self.dims)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -76,9 +76,14 @@ class SemanticEncoder:
         assert input_sample_rate in (16000, 48000)
         self._plans: dict = {}
         d = self.dims
-        self.mel_pad = torch.empty((batch, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16, device=self.device)
-        self.mel_scratch = torch.empty((batch, self.whisper.frontend.frames_alloc, d.n_mels), dtype=torch.float32,
-                                       device=self.device)
+        # the encoder is compute-bound and runs in micro-batches of `enc_chunk` windows (bounded workspace);
+        # the decoder is latency/memory-bound and steps all `batch` windows at once so its per-step fixed
+        # costs are amortised over as many streams as fit
+        self.enc_chunk = min(enc_chunk, batch)
+        self.mel_pad = torch.empty((self.enc_chunk, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16,
+                                   device=self.device)
+        self.mel_scratch = torch.empty((self.enc_chunk, self.whisper.frontend.frames_alloc, d.n_mels),
+                                       dtype=torch.float32, device=self.device)
         self.enc_out = torch.empty((batch, d.n_audio_ctx, d.n_audio_state), dtype=torch.bfloat16, device=self.device)
         self._pros_out = None
 
@@ -93,7 +98,8 @@ class SemanticEncoder:
         return p
 
     def kernels_per_step(self) -> int:
-        enc = 2 + 7 * self.dims.n_audio_layer + 1 + 2 + 2  # stem, layers, ln_post, 2 memsets, 2 logmel
+        n_chunks = -(-self.batch // self.enc_chunk)
+        enc = n_chunks * (2 + 7 * self.dims.n_audio_layer + 1 + 2)  # stem, layers, ln_post, 2 logmel kernels
         dec = 1 + self.session.n_steps * self.session.kernels_per_step
         return enc + dec + 2
 
@@ -103,10 +109,19 @@ class SemanticEncoder:
         assert len(lengths) == self.batch
         plan, offs, lens, pros_out = self._plan(tuple(lengths))
         self.prosody.run(pcm, plan, out=pros_out)
-        self.whisper.frontend(pcm, offs, lens, decim=self.decim, scratch=self.mel_scratch, out_bf16=self.mel_pad)
-        self.whisper.encode(self.mel_pad, out=self.enc_out)
+        self.encode_windows(pcm, offs, lens)
         tokens, sum_lp = self.session.decode(self.enc_out)
         return EncodeResult(tokens, sum_lp, pros_out["tags"])
+
+    def encode_windows(self, pcm: torch.Tensor, offs: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
+        """K1 + K2 over all windows in micro-batches; fills self.enc_out [batch, n_ctx, d]."""
+        for c0 in range(0, self.batch, self.enc_chunk):
+            c1 = min(c0 + self.enc_chunk, self.batch)
+            n = c1 - c0
+            self.whisper.frontend(pcm, offs[c0:c1], lens[c0:c1], decim=self.decim, scratch=self.mel_scratch[:n],
+                                  out_bf16=self.mel_pad[:n])
+            self.whisper.encode(self.mel_pad[:n], out=self.enc_out[c0:c1])
+        return self.enc_out
 
     def to_packets(self, tokens_host: np.ndarray, tags_host: np.ndarray, timestamps=None,
                    mode: JanusMode = JanusMode.SEMANTIC_VOICE, override_emotion=None):
