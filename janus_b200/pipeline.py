@@ -143,3 +143,21 @@ class SemanticEncoder:
             tok = res.tokens.cpu().numpy()
             tags = res.tags.cpu().numpy()
         return self.to_packets(tok, tags, timestamps)
+
+
+def gather_packets(local_packets: list, local_stream_ids: list[int], dst: int = 0):
+    """Host-side gather of the per-rank packet bytes (55-500 B each) onto rank `dst`, ordered by global
+    stream id. This is the only cross-rank step of the path and it is not on the GPU data path: an
+    NCCL collective over NVLink for a few KB would be pure latency."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return dict(zip(local_stream_ids, local_packets))
+    payload = list(zip(local_stream_ids, local_packets))
+    gathered = [None] * dist.get_world_size() if dist.get_rank() == dst else None
+    dist.gather_object(payload, gathered, dst=dst)
+    if dist.get_rank() != dst:
+        return None
+    out = {}
+    for part in gathered:
+        out.update(dict(part))
+    return dict(sorted(out.items()))

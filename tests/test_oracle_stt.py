@@ -1,0 +1,126 @@
+"""Pins the STT oracles (no GPU): the numpy log-mel restatement against the independent HF
+WhisperFeatureExtractor, and the fp32 Whisper restatement against HF transformers' Whisper with the
+same weights. (faster-whisper / CTranslate2 themselves are not installable offline: parity unpinned.)"""
+import numpy as np
+import pytest
+import torch
+
+from janus_b200.synth import make_clips
+from janus_b200.whisper.config import PRESETS, detokenize, test_dims, tokenizer_spec
+from janus_b200.whisper.weights import init_random_weights
+from oracle import whisper_ref as R
+from oracle.logmel_ref import log_mel_utterance, log_mel_window, mel_filters
+
+transformers = pytest.importorskip("transformers")
+
+
+def test_logmel_matches_hf_feature_extractor():
+    x = make_clips(1, 30.0, 16000, seed=3).numpy()[0]
+    ours = log_mel_window(x, 80)
+    fe = transformers.WhisperFeatureExtractor(feature_size=80)
+    hf = fe(x, sampling_rate=16000, return_tensors="np").input_features[0]
+    assert ours.shape == hf.shape == (80, 3000)
+    # identical away from the tail (HF reflects at 30 s, faster-whisper sees 160 zeros first)
+    assert np.abs(ours[:, :2990] - hf[:, :2990]).max() < 5e-5
+    assert np.abs(fe.mel_filters.T - mel_filters(80)).max() < 1e-6
+
+
+def test_logmel_window_semantics():
+    x = make_clips(1, 30.0, 16000, seed=3).numpy()[0]
+    full = log_mel_utterance(x[:80000], 80)
+    assert full.shape == (80, 501)                      # (80000 + 160) // 160 frames kept
+    win = log_mel_window(x[:80000], 80)
+    assert win.shape == (80, 3000)
+    assert np.array_equal(win[:, :500], full[:, :500])  # content_frames = 500
+    assert (win[:, 500:] == 0).all()                    # zero padding in FEATURE space
+    assert full.min() >= full.max() - 2.0 - 1e-6        # (max - 8 + 4)/4 clamp -> dynamic range 2.0
+
+
+def _to_hf(W, dims):
+    cfg = transformers.WhisperConfig(
+        vocab_size=dims.n_vocab, num_mel_bins=dims.n_mels, d_model=dims.d, encoder_layers=dims.n_audio_layer,
+        decoder_layers=dims.n_text_layer, encoder_attention_heads=dims.n_audio_head,
+        decoder_attention_heads=dims.n_text_head, encoder_ffn_dim=4 * dims.d, decoder_ffn_dim=4 * dims.d,
+        max_source_positions=dims.n_audio_ctx, max_target_positions=dims.n_text_ctx,
+        activation_function="gelu", attn_implementation="eager")
+    m = transformers.WhisperForConditionalGeneration(cfg).eval()
+    sd = {}
+
+    def ln(hp, p):
+        sd[hp + ".weight"], sd[hp + ".bias"] = W[p + ".w"], W[p + ".b"]
+
+    def attn(hp, p):
+        for a, b in (("q_proj", "q"), ("k_proj", "k"), ("v_proj", "v"), ("out_proj", "o")):
+            sd[f"{hp}.{a}.weight"] = W[f"{p}.{b}.w"]
+            if b != "k":
+                sd[f"{hp}.{a}.bias"] = W[f"{p}.{b}.b"]
+
+    def mlp(hp, p):
+        sd[hp + ".fc1.weight"], sd[hp + ".fc1.bias"] = W[p + ".mlp.fc1.w"], W[p + ".mlp.fc1.b"]
+        sd[hp + ".fc2.weight"], sd[hp + ".fc2.bias"] = W[p + ".mlp.fc2.w"], W[p + ".mlp.fc2.b"]
+
+    sd["model.encoder.conv1.weight"], sd["model.encoder.conv1.bias"] = W["enc.conv1.w"], W["enc.conv1.b"]
+    sd["model.encoder.conv2.weight"], sd["model.encoder.conv2.bias"] = W["enc.conv2.w"], W["enc.conv2.b"]
+    sd["model.encoder.embed_positions.weight"] = W["enc.pos"]
+    for i in range(dims.n_audio_layer):
+        hp, p = f"model.encoder.layers.{i}", f"enc.l{i}"
+        attn(hp + ".self_attn", p + ".attn"); ln(hp + ".self_attn_layer_norm", p + ".attn_ln")
+        mlp(hp, p); ln(hp + ".final_layer_norm", p + ".mlp_ln")
+    ln("model.encoder.layer_norm", "enc.ln_post")
+    sd["model.decoder.embed_tokens.weight"] = W["dec.tok_emb"]
+    sd["model.decoder.embed_positions.weight"] = W["dec.pos"]
+    for i in range(dims.n_text_layer):
+        hp, p = f"model.decoder.layers.{i}", f"dec.l{i}"
+        attn(hp + ".self_attn", p + ".attn"); ln(hp + ".self_attn_layer_norm", p + ".attn_ln")
+        attn(hp + ".encoder_attn", p + ".cross"); ln(hp + ".encoder_attn_layer_norm", p + ".cross_ln")
+        mlp(hp, p); ln(hp + ".final_layer_norm", p + ".mlp_ln")
+    ln("model.decoder.layer_norm", "dec.ln")
+    sd["proj_out.weight"] = W["dec.tok_emb"]
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not missing and not unexpected
+    return m
+
+
+def test_whisper_oracle_matches_hf_transformers():
+    dims = test_dims(d=128, heads=2, layers=2)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=1, profile="diverse")
+    torch.manual_seed(0)
+    mel = torch.randn(2, 80, 3000) * 0.5
+    enc = R.encode(W, dims, mel)
+    hf = _to_hf(W, dims)
+    with torch.no_grad():
+        henc = hf.model.encoder(mel).last_hidden_state
+        assert float((henc - enc).abs().max()) < 2e-5
+        toks = torch.tensor([[spec.sot, spec.lang_en, spec.transcribe, spec.timestamp_begin, 100, 2000, 31000]] * 2)
+        hl = hf(input_features=mel, decoder_input_ids=toks).logits
+    st = R.DecoderState(W, dims, enc)
+    ol = torch.cat([st.step(toks[:, :3]), st.step(toks[:, 3:4]), st.step(toks[:, 4:])], 1)  # KV-cache path
+    assert float((hl - ol).abs().max()) < 2e-3 * max(1.0, float(ol.abs().max()))
+
+
+def test_greedy_rules():
+    dims = test_dims(d=128, heads=2, layers=2)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=3, profile="diverse")
+    mel = torch.randn(1, 80, 3000) * 0.5
+    out, lp, mg = R.greedy_decode(W, dims, spec, R.encode(W, dims, mel), 24, return_margins=True)
+    seq = out[0].tolist()
+    tb = spec.timestamp_begin
+    assert tb <= seq[0] <= tb + spec.max_initial_timestamp_index      # first token: timestamp <= 1.0 s
+    assert seq[1] < tb                                                 # ... followed by text (or eot)
+    stamps = [t for t in seq if t >= tb]
+    assert stamps == sorted(stamps)                                    # timestamps never decrease
+    sup = set(spec.suppress_ids)
+    assert not any(t in sup for t in seq)
+    assert detokenize(seq, spec).count(" w") == sum(1 for t in seq if t < spec.eot)
+
+
+def test_presets_param_counts():
+    # architecture sanity: parameter counts of the named models (tiny 37.8 M, small ~242 M)
+    for name, lo, hi in (("tiny", 37e6, 39e6), ("small", 240e6, 245e6)):
+        d = PRESETS[name]
+        n = d.n_audio_state
+        enc = d.n_mels * n * 3 + n + 3 * n * n + n + d.n_audio_layer * (4 * n * n + 3 * n + 8 * n * n + 5 * n + 4 * n) + 2 * n
+        dec = d.n_vocab * n + 448 * n + d.n_text_layer * (8 * n * n + 6 * n + 8 * n * n + 5 * n + 6 * n) + 2 * n
+        assert lo < enc + dec < hi, (name, enc + dec)
