@@ -17,8 +17,11 @@ def stt_config(args, batch: int) -> dict:
         "workload": f"Whisper-{args.model} (random-init, bf16) log-mel + encoder + greedy decode of "
                     f"{args.max_new_tokens} tokens per 30 s window, plus aubio-equivalent YIN pitch / RMS prosody "
                     "on the same windows -> MessagePack packets (BASELINE configs[2] + prosody)",
-        "windows_per_gpu": batch, "encoder_micro_batch": min(64, batch), "clip_seconds": args.clip_seconds, "sample_rate": args.sample_rate,
-        "max_new_tokens": args.max_new_tokens,
+        "windows_per_gpu": batch, "lane_batch": min(args.lane_batch, batch), "clip_seconds": args.clip_seconds,
+        "sample_rate": args.sample_rate, "max_new_tokens": args.max_new_tokens,
+        "pipeline": "per call: windows split into lanes of lane_batch; encoder stream (prosody, log-mel, encoder, "
+                    "cross-KV) runs lane by lane while earlier lanes decode on their own streams; calls are enqueued "
+                    "back to back and fully drained inside the timed region",
         "parallelism": f"dp{args.gpus} over independent windows, no collective",
         "l2": "per-step working set (cross-KV 3.5 GB + activations) is far larger than the 126 MB L2",
     }
@@ -123,7 +126,8 @@ def run_gpu_stt(args) -> None:
         torch.cuda.synchronize()
 
     enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
-                          prosody_sample_rate=sr, input_sample_rate=sr)
+                          prosody_sample_rate=sr, input_sample_rate=sr, lane_batch=args.lane_batch,
+                          n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph)
     N = int(round(seconds * sr))
     x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)
     lengths = tuple([N] * B)
@@ -131,84 +135,128 @@ def run_gpu_stt(args) -> None:
     def step_device():
         return enc.encode_device(x, lengths)
 
+    def drain():
+        enc.synchronize()
+        barrier()
+
+    # ---- device-resident throughput ("value"): K calls enqueued back to back, drained inside the
+    # timed region. Every call's prosody + log-mel + encoder + cross-KV + decode runs to completion.
     W_ = max(args.warmup, 3)
     for _ in range(W_):
         step_device()
-    barrier()
+    drain()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
+    res = None
     for _ in range(args.steps):
-        step_device()
+        res = step_device()
+    for lane in enc.lanes:             # join every lane + the encoder stream into the timing stream
+        torch.cuda.current_stream(dev).wait_stream(lane.stream)
+    torch.cuda.current_stream(dev).wait_stream(enc.enc_stream)
     e1.record()
-    barrier()
+    drain()
     ms_total = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- stage breakdown (device time, one step, events between stages)
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
-    plan, offs, lens, pros_out = enc._plan(lengths)
+    # ---- stage breakdown: each stage ALONE on one stream (no overlap), one step's worth of work
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    lb = enc.lane_batch
+    ll = lengths[:lb]
+    plan, offs, lens = enc._lane_plan(ll)
     ev[0].record()
-    enc.prosody.run(x, plan, out=pros_out)
+    for j in range(enc.lanes_per_call):
+        enc.prosody.run(x[j * lb * N:(j + 1) * lb * N], plan, out=enc.lanes[j].pros_out[ll])
     ev[1].record()
-    ev[2].record()   # (log-mel is interleaved with the encoder micro-batches; timed together)
-    enc.encode_windows(x, offs, lens)
+    for j in range(enc.lanes_per_call):
+        enc.whisper.frontend(x[j * lb * N:(j + 1) * lb * N], offs, lens, decim=enc.decim, scratch=enc.mel_scratch,
+                             out_bf16=enc.mel_pad)
+        enc.whisper.encode(enc.mel_pad, out=enc.enc_out)
+    ev[2].record()
+    for j in range(enc.lanes_per_call):
+        enc.lanes[j].session.cross_kv(enc.enc_out)
     ev[3].record()
-    enc.session.cross_kv(enc.enc_out)
+    for j in range(enc.lanes_per_call):
+        enc.lanes[j].session.reset()
+        enc.lanes[j].session.run_steps()
     ev[4].record()
-    enc.session.reset()
-    for _ in range(enc.session.n_steps):
-        enc.session.graph.replay()
-    ev[5].record()
     torch.cuda.synchronize()
     stages = {k: ev[i].elapsed_time(ev[i + 1]) for i, k in
-              enumerate(["prosody_ms", "_", "logmel_encoder_ms", "cross_kv_ms", "decoder_ms"]) if k != "_"}
+              enumerate(["prosody_ms", "logmel_encoder_ms", "cross_kv_ms", "decoder_serial_ms"])}
+    # decode of all lanes of one call running concurrently, nothing else on the GPU
+    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    cur = torch.cuda.current_stream(dev)
+    for j in range(enc.lanes_per_call):
+        ln = enc.lanes[j]
+        ln.stream.wait_stream(cur)
+        with torch.cuda.stream(ln.stream):
+            ln.session.reset()
+            ln.session.run_steps()
+    for j in range(enc.lanes_per_call):
+        cur.wait_stream(enc.lanes[j].stream)
+    b_.record()
+    torch.cuda.synchronize()
+    stages["decoder_concurrent_lanes_ms"] = a.elapsed_time(b_)
 
-    # ---- dominant kernel alone: decode-time cross-attention (HBM-bound), per launch over all layers
+    # ---- dominant kernel alone: decode-time cross-attention (HBM-bound), per launch over all layers,
+    # at the launch shape the pipeline uses (one lane's windows)
     ses = enc.session
     d = enc.dims
     stream = torch.cuda.current_stream(dev)
     k_ms = []
-    for rep in range(3):
+    for rep in range(4):
         a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
-        for l in range(d.n_text_layer):
-            _abi.call("janus_dec_cross_attn_bf16", ses.q.data_ptr(), ses.cross_k[l].data_ptr(), ses.cross_v[l].data_ptr(),
-                      ses.att.data_ptr(), B, d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld, stream.cuda_stream)
+        for ln in enc.lanes[:enc.lanes_per_call]:
+            s_ = ln.session
+            for l in range(d.n_text_layer):
+                _abi.call("janus_dec_cross_attn_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(), s_.cross_v[l].data_ptr(),
+                          s_.att.data_ptr(), lb, d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld, stream.cuda_stream)
         b_.record(stream)
         torch.cuda.synchronize()
         if rep:
-            k_ms.append(a.elapsed_time(b_) / d.n_text_layer)
+            k_ms.append(a.elapsed_time(b_) / (d.n_text_layer * enc.lanes_per_call))
     xattn_ms = float(np.mean(k_ms))
 
-    # ---- end to end: pinned host PCM -> H2D -> all kernels -> D2H tokens/tags -> detokenise -> packets
+    # ---- end to end: pinned host PCM -> H2D -> all kernels -> D2H tokens/tags -> detokenise -> packets.
+    # Call k is enqueued before the host finishes call k-1 (D2H + MessagePack), so host work overlaps the GPU.
     host = torch.empty(x.numel(), dtype=torch.float32, pin_memory=True)
     host.copy_(x)
-    xd = torch.empty_like(x)
-    tok_host = torch.empty((B, ses.max_new), dtype=torch.int32, pin_memory=True)
+    xd = [torch.empty_like(x) for _ in range(2)]
+    tok_host = torch.empty((B, enc.max_new), dtype=torch.int32, pin_memory=True)
     tag_host = torch.empty((B, 2), dtype=torch.uint8, pin_memory=True)
+    copy_stream = torch.cuda.Stream(dev)
     n_pkts = 0
 
-    def step_e2e():
+    def finish(r):
         nonlocal n_pkts
-        xd.copy_(host, non_blocking=True)
-        r = enc.encode_device(xd, lengths)
-        tok_host.copy_(r.tokens, non_blocking=True)
-        tag_host.copy_(r.tags, non_blocking=True)
-        torch.cuda.current_stream(dev).synchronize()
+        with torch.cuda.stream(copy_stream):
+            r.wait(copy_stream)
+            tok_host.copy_(r.tokens, non_blocking=True)
+            tag_host.copy_(r.tags, non_blocking=True)
+        copy_stream.synchronize()
         texts, pk = enc.to_packets(tok_host.numpy(), tag_host.numpy(), timestamps=[0.0] * B)
         n_pkts = sum(p is not None for p in pk)
 
+    def run_e2e(k):
+        prev = None
+        for i in range(k):
+            r = enc.encode_device(xd[i & 1], lengths, host_pcm=host)
+            if prev is not None:
+                finish(prev)
+            prev = r
+        finish(prev)
+
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    step_e2e()
-    barrier()
+    run_e2e(2)
+    drain()
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        step_e2e()
-    barrier()
+    run_e2e(e2e_steps)
+    drain()
     e2e_ms = (time.perf_counter() - t0) * 1e3
 
     t = torch.tensor([ms_total, e2e_ms, xattn_ms], dtype=torch.float64, device=dev)
@@ -228,7 +276,7 @@ def run_gpu_stt(args) -> None:
             hbm_peak, tf_peak, peak_src = 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
         H, T, kv_ld = d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld
         # algorithmic bytes of one cross-attention launch: K and V of every (stream, head) once, q in, out out
-        alg_bytes = B * H * (2 * T * 64 * 2) + 2 * B * d.n_text_state * 2
+        alg_bytes = lb * H * (2 * T * 64 * 2) + 2 * lb * d.n_text_state * 2
         achieved = alg_bytes / (xattn_ms / 1e3) / 1e9
         # encoder tensor-pipe figure for context (SURVEY 8d FLOP count)
         dd, L, Ta = d.n_audio_state, d.n_audio_layer, d.n_audio_ctx
@@ -246,7 +294,7 @@ def run_gpu_stt(args) -> None:
             "roofline": {"kernel": "dec_cross_attn_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
                          "kernel_ms": xattn_ms, "algorithmic_bytes_per_launch": alg_bytes,
-                         "launches_per_step": d.n_text_layer * ses.n_steps,
+                         "launches_per_step": d.n_text_layer * ses.n_steps * enc.lanes_per_call,
                          "encoder_tensor": {"tflops": enc_flops / (stages["logmel_encoder_ms"] / 1e3) / 1e12,
                                             "peak": tf_peak, "frac": enc_flops / (stages["logmel_encoder_ms"] / 1e3) / 1e12 / tf_peak,
                                             "algorithmic_flops": enc_flops}},

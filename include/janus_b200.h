@@ -45,6 +45,9 @@ int32_t janus_abi_version(void);
 const char* janus_last_error(void);
 /* 0 when device `dev` can run the kernels (compute capability 10.x), else JANUS_ERR_UNSUPPORTED. */
 int32_t janus_check_device(int32_t dev);
+/* Programmatic dependent launch for the decode-step kernel chain (default on). 0 launches the same
+ * kernels fully serialised; returns the previous setting. Process-global; meant for A/B measurements. */
+int32_t janus_set_pdl(int32_t enabled);
 
 /* ------------------------------------------------------------------------------------------
  * K4: YIN pitch + per-hop level (bit-exact restatement of aubio's float32 arithmetic)
@@ -101,6 +104,9 @@ int32_t janus_gemm_bf16(const void* A, int64_t lda, int64_t a_batch_stride, cons
 int32_t janus_layernorm_bf16(const void* x, const float* w, const float* b, void* y, int64_t rows, int32_t d,
                              void* stream);
 /* Fused non-causal attention over packed qkv bf16 [n_batch, T, 3*64*n_heads] -> out bf16 [n_batch, T, 64*n_heads]. */
+/* Diagnostic: n dependent LayerNorm launches (PDL chain) issued from C; used to measure launch latency. */
+int32_t janus_debug_ln_chain(const void* x, const float* w, const float* b, void* y, int64_t rows, int32_t d,
+                             int32_t n, void* stream);
 int32_t janus_attention_enc_bf16(const void* qkv, void* out, int32_t n_batch, int32_t T, int32_t n_heads,
                                  void* stream);
 
@@ -179,8 +185,18 @@ typedef struct {
   int32_t eot, blank, timestamp_begin, max_initial_timestamp_index;
 } janus_decoder_weights_t;
 
+/* JANUS_DECODE_LIGHT: run every linear layer of the step through the register-streaming kernel (no
+ * TMEM, < 32 KB shared memory) so that the step can share SMs with the tcgen05 encoder kernels of
+ * another stream; requires batch <= 64. */
+#define JANUS_DECODE_LIGHT 1
+/* JANUS_DECODE_FUSED: everything between two cross-attentions runs as one persistent kernel with grid-wide
+ * barriers (dec_fused.cu) instead of one kernel per op; needs state->barrier. At most one fused decode
+ * chain may be in flight per device at a time (its CTAs wait on each other). */
+#define JANUS_DECODE_FUSED 2
+
 typedef struct {
   int32_t batch, max_len, n_prompt;    /* max_len = n_prompt + max_new_tokens */
+  int32_t flags;                       /* JANUS_DECODE_* */
   int32_t* tokens;                     /* [batch, max_len]; the sot prompt is pre-filled by the caller */
   const int32_t* forced;               /* [batch, max_len] teacher forcing (-1 = free) or NULL */
   int32_t* choice;                     /* [batch, max_len] argmax under the rules (diagnostic) or NULL */
@@ -194,6 +210,7 @@ typedef struct {
   const void* cross_v;                 /* bf16 [L, batch, H, n_ctx, 64] */
   void* x; void* xn; void* qkv; void* att; void* q; void* ff;  /* bf16 [batch, d|d|3d|d|d|4d] */
   float* logits;                       /* fp32 [batch, n_vocab_pad] */
+  uint64_t* barrier;                   /* device counter for JANUS_DECODE_FUSED (zero-initialised once), else NULL */
 } janus_decode_state_t;
 
 /* Skinny linear layer of the decode step: out[r, n] = act(sum_k A[r,k] W[n,k] + bias[n]) (+ residual[r,n]),

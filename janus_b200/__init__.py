@@ -7,3 +7,10 @@ There is no CPU fallback: importing the service classes without the built librar
 them without an sm_100 device, raises.
 """
 __version__ = "0.1.0"
+
+import os as _os
+
+# The batched engine runs one encoder stream plus up to ~16 decode-lane streams concurrently; with the
+# default of 8 hardware work queues independent streams would be serialised behind each other.
+# Must be set before the CUDA context is created (harmless otherwise).
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")

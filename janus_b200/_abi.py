@@ -24,12 +24,14 @@ SIGNATURES = {
     "janus_abi_version": (_I32, []),
     "janus_last_error": (_c.c_char_p, []),
     "janus_check_device": (_I32, [_I32]),
+    "janus_set_pdl": (_I32, [_I32]),
     "janus_yin_frames_per_group": (_I32, []),
     "janus_yin_frames_f32": (_I32, [_P, _P, _P, _P, _P, _I32, _I64, _I32, _I32, _I32, _F32, _F32,
                                     _P, _P, _P, _P, _P]),
     "janus_yin_state_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     "janus_prosody_reduce_f32": (_I32, [_P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P]),
     "janus_layernorm_bf16": (_I32, [_P, _P, _P, _P, _I64, _I32, _P]),
+    "janus_debug_ln_chain": (_I32, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),
     "janus_attention_enc_bf16": (_I32, [_P, _P, _I32, _I32, _I32, _P]),
     "janus_logmel_frames_alloc": (_I32, []),
     "janus_logmel_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _P, _P, _P, _P]),

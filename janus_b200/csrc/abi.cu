@@ -9,7 +9,14 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+int g_pdl_enabled = 1;
 }  // namespace janus
+
+extern "C" int32_t janus_set_pdl(int32_t enabled) {
+  const int prev = janus::g_pdl_enabled;
+  janus::g_pdl_enabled = enabled != 0;
+  return prev;
+}
 
 extern "C" int32_t janus_abi_version(void) { return JANUS_ABI_VERSION; }
 extern "C" const char* janus_last_error(void) { return janus::g_err; }

@@ -24,37 +24,43 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-constexpr int DL_WARPS = 4;       // 2 column tiles x 2 K halves
-constexpr int DL_COLS = 16;       // output columns per CTA
+constexpr int DL_COLS = 16;       // output columns per CTA (2 column tiles of 8)
 
-template <int MT>
-__global__ void __launch_bounds__(DL_WARPS * 32)
-dec_linear_kernel(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloat16* __restrict__ W,
-                  const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual, void* __restrict__ out,
+// MT = 16-row tiles of A, KS = number of warps splitting K for each column tile (2 for K <= 1024,
+// 8 for the K = 4d MLP down-projection so every warp still streams ~12 32-wide k blocks)
+template <int MT, int KS>
+__global__ void __launch_bounds__(2 * KS * 32)
+dec_linear_kernel(const __nv_bfloat16* A, int lda, const __nv_bfloat16* __restrict__ W,
+                  const float* __restrict__ bias, const __nv_bfloat16* residual, void* out,
                   int rows, int N, int K, int act, int out_f32) {
-  __shared__ float red[2][MT][32][4];
+  __shared__ float red[KS - 1][2][MT][32][4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ct = warp & 1, kh = warp >> 1;
   const int g = lane >> 2, t4 = lane & 3;
   const int n0 = blockIdx.x * DL_COLS + ct * 8;
   const int kblocks = K >> 5;
-  const int kb0 = kh * (kblocks >> 1), kb1 = kh ? kblocks : (kblocks >> 1);
+  const int kper = (kblocks + KS - 1) / KS;
+  const int kb0 = kh * kper, kb1 = min(kblocks, kb0 + kper);
   float acc[MT][4];
 #pragma unroll
   for (int m = 0; m < MT; ++m) acc[m][0] = acc[m][1] = acc[m][2] = acc[m][3] = 0.f;
   const uint4* wp = reinterpret_cast<const uint4*>(W + (long long)(n0 + g) * K + 8 * t4);
   const bool col_ok = n0 + g < N;
   // Issue a whole batch of weight loads before touching them: the op is one DRAM round trip, so
-  // what matters is how many bytes are in flight, not how fast they are consumed.
+  // what matters is how many bytes are in flight, not how fast they are consumed. The first batch
+  // is requested BEFORE the grid dependency resolves (PDL): the weights are immutable, so their DRAM
+  // latency hides behind the producer kernel's tail; A / residual are only touched after pdl_wait().
   constexpr int PF = MT <= 4 ? 12 : (MT <= 8 ? 8 : 4);
+  uint4 wv[PF];
+#pragma unroll
+  for (int i = 0; i < PF; ++i) {
+    wv[i] = make_uint4(0, 0, 0, 0);
+    if (col_ok && kb0 + i < kb1) wv[i] = __ldg(wp + (kb0 + i) * 4);  // 32 k = 64 B = 4 uint4 per row
+  }
+  pdl_launch_dependents();
+  pdl_wait();
 #pragma unroll 1
   for (int kbase = kb0; kbase < kb1; kbase += PF) {
-    uint4 wv[PF];
-#pragma unroll
-    for (int i = 0; i < PF; ++i) {
-      wv[i] = make_uint4(0, 0, 0, 0);
-      if (col_ok && kbase + i < kb1) wv[i] = __ldg(wp + (kbase + i) * 4);  // 32 k = 64 B = 4 uint4 per row
-    }
 #pragma unroll
     for (int i = 0; i < PF; ++i) {
       const int kb = kbase + i;
@@ -63,22 +69,35 @@ dec_linear_kernel(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloa
         for (int m = 0; m < MT; ++m) {
           const int r0 = 16 * m + g, r1 = r0 + 8;
           uint4 a_lo = make_uint4(0, 0, 0, 0), a_hi = make_uint4(0, 0, 0, 0);
-          if (r0 < rows) a_lo = __ldg(reinterpret_cast<const uint4*>(A + (long long)r0 * lda + kb * 32 + 8 * t4));
-          if (r1 < rows) a_hi = __ldg(reinterpret_cast<const uint4*>(A + (long long)r1 * lda + kb * 32 + 8 * t4));
+          if (r0 < rows) a_lo = *reinterpret_cast<const uint4*>(A + (long long)r0 * lda + kb * 32 + 8 * t4);
+          if (r1 < rows) a_hi = *reinterpret_cast<const uint4*>(A + (long long)r1 * lda + kb * 32 + 8 * t4);
           mma_bf16_16816(acc[m], a_lo.x, a_hi.x, a_lo.y, a_hi.y, wv[i].x, wv[i].y);
           mma_bf16_16816(acc[m], a_lo.z, a_hi.z, a_lo.w, a_hi.w, wv[i].z, wv[i].w);
         }
       }
     }
+    if (kbase + PF < kb1) {
+#pragma unroll
+      for (int i = 0; i < PF; ++i) {
+        wv[i] = make_uint4(0, 0, 0, 0);
+        if (col_ok && kbase + PF + i < kb1) wv[i] = __ldg(wp + (kbase + PF + i) * 4);
+      }
+    }
   }
-  if (kh == 1) {
+  if (kh > 0) {
 #pragma unroll
     for (int m = 0; m < MT; ++m)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) red[ct][m][lane][i] = acc[m][i];
+      *reinterpret_cast<float4*>(red[kh - 1][ct][m][lane]) = make_float4(acc[m][0], acc[m][1], acc[m][2], acc[m][3]);
   }
   __syncthreads();
-  if (kh == 1) return;
+  if (kh > 0) return;
+#pragma unroll
+  for (int s = 0; s < KS - 1; ++s)      // fixed summation order: deterministic
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const float4 r4 = *reinterpret_cast<const float4*>(red[s][ct][m][lane]);
+      acc[m][0] += r4.x; acc[m][1] += r4.y; acc[m][2] += r4.z; acc[m][3] += r4.w;
+    }
   const int col = n0 + 2 * t4;
   if (col >= N) return;
   float b0 = 0.f, b1 = 0.f;
@@ -89,8 +108,8 @@ dec_linear_kernel(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloa
     for (int half = 0; half < 2; ++half) {
       const int r = 16 * m + g + 8 * half;
       if (r >= rows) continue;
-      float v0 = acc[m][2 * half] + red[ct][m][lane][2 * half] + b0;
-      float v1 = acc[m][2 * half + 1] + red[ct][m][lane][2 * half + 1] + b1;
+      float v0 = acc[m][2 * half] + b0;
+      float v1 = acc[m][2 * half + 1] + b1;
       if (act == ACT_GELU) { v0 = gelu_erf(v0); v1 = gelu_erf(v1); }
       const long long o = (long long)r * N + col;
       if (residual) {
@@ -105,18 +124,30 @@ dec_linear_kernel(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloa
 
 int dec_linear(const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, const float* bias,
                const __nv_bfloat16* residual, void* out, int rows, int N, int K, int act, int out_f32,
-               cudaStream_t stream) {
-  JANUS_CHECK_ARG(K % 64 == 0 && N % 2 == 0 && lda % 8 == 0, "dec_linear: K %% 64, N %% 2, lda %% 8 required");
+               cudaStream_t stream, bool pdl) {
+  JANUS_CHECK_ARG(K % 32 == 0 && N % 2 == 0 && lda % 8 == 0, "dec_linear: K %% 32, N %% 2, lda %% 8 required");
   JANUS_CHECK_ARG(rows > 0 && rows <= 256, "dec_linear: 1..256 rows supported (got %d)", rows);
   const int grid = (N + DL_COLS - 1) / DL_COLS;
   const int mt = (rows + 15) / 16;
-#define DL_LAUNCH(MT)                                                                                              \
-  dec_linear_kernel<MT><<<grid, DL_WARPS * 32, 0, stream>>>(A, lda, W, bias, residual, out, rows, N, K, act, out_f32)
-  if (mt <= 1) DL_LAUNCH(1);
-  else if (mt <= 2) DL_LAUNCH(2);
-  else if (mt <= 4) DL_LAUNCH(4);
-  else if (mt <= 8) DL_LAUNCH(8);
-  else DL_LAUNCH(16);
+#define DL_LAUNCH(MT, KS)                                                                                          \
+  do {                                                                                                             \
+    if (pdl) {                                                                                                     \
+      JANUS_CUDA(launch_pdl(dec_linear_kernel<MT, KS>, dim3(grid), dim3(2 * KS * 32), 0, stream, A, lda, W, bias,    \
+                            residual, out, rows, N, K, act, out_f32));                                             \
+    } else {                                                                                                       \
+      dec_linear_kernel<MT, KS><<<grid, 2 * KS * 32, 0, stream>>>(A, lda, W, bias, residual, out, rows, N, K, act,  \
+                                                                  out_f32);                                        \
+    }                                                                                                              \
+  } while (0)
+  if (K > 1024 && mt <= 4) {   // long K (MLP down-projection): 8-way K split
+    if (mt <= 1) DL_LAUNCH(1, 8);
+    else if (mt <= 2) DL_LAUNCH(2, 8);
+    else DL_LAUNCH(4, 8);
+  } else if (mt <= 1) DL_LAUNCH(1, 2);
+  else if (mt <= 2) DL_LAUNCH(2, 2);
+  else if (mt <= 4) DL_LAUNCH(4, 2);
+  else if (mt <= 8) DL_LAUNCH(8, 2);
+  else DL_LAUNCH(16, 2);
 #undef DL_LAUNCH
   JANUS_LAUNCH_CHECK("dec_linear_kernel");
   return JANUS_OK;
@@ -130,5 +161,5 @@ extern "C" int32_t janus_dec_linear_bf16(const void* A, int32_t lda, const void*
   JANUS_CHECK_ARG(A && W && out, "dec_linear: null pointer");
   return janus::dec_linear(static_cast<const __nv_bfloat16*>(A), lda, static_cast<const __nv_bfloat16*>(W), bias,
                            static_cast<const __nv_bfloat16*>(residual), out, rows, N, K, act, out_f32,
-                           (cudaStream_t)stream);
+                           (cudaStream_t)stream, true);
 }

@@ -26,10 +26,14 @@ constexpr int DH = 64;
 // ------------------------------------------------------------------------------------------
 // embedding
 // ------------------------------------------------------------------------------------------
-__global__ void dec_embed_kernel(const int32_t* __restrict__ tokens, int max_len, const int32_t* __restrict__ pos_p,
+// (mutable operands of the PDL chain -- tokens, pos, activations, KV caches -- carry no __restrict__ so
+// they are never read through the non-coherent path; see common.cuh)
+__global__ void dec_embed_kernel(const int32_t* tokens, int max_len, const int32_t* pos_p,
                                  const __nv_bfloat16* __restrict__ emb, const float* __restrict__ pos_emb, int d,
-                                 __nv_bfloat16* __restrict__ x) {
+                                 __nv_bfloat16* x) {
   const int b = blockIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
   const int pos = *pos_p;
   const int tok = tokens[(long long)b * max_len + pos];
   const __nv_bfloat16* e = emb + (long long)tok * d;
@@ -42,12 +46,13 @@ __global__ void dec_embed_kernel(const int32_t* __restrict__ tokens, int max_len
 // causal self-attention over the KV cache: one warp per (head, stream)
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32)
-dec_self_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ kc,
-                     __nv_bfloat16* __restrict__ vc, const int32_t* __restrict__ pos_p, int d, int n_ctx,
-                     __nv_bfloat16* __restrict__ out) {
+dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos_p, int d,
+                     int n_ctx, __nv_bfloat16* out) {
   __shared__ float ps[512];
   __shared__ float qs[DH];
   const int h = blockIdx.x, b = blockIdx.y, H = gridDim.x, lane = threadIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
   const int pos = *pos_p;
   const __nv_bfloat16* row = qkv + (long long)b * 3 * d + h * DH;
   __nv_bfloat16* K = kc + ((long long)b * H + h) * n_ctx * DH;
@@ -105,14 +110,16 @@ dec_self_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __res
 constexpr int XA_THREADS = 192;  // 192 * 8 keys = 1536 >= 1500
 
 __global__ void __launch_bounds__(XA_THREADS)
-dec_cross_attn_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ kT,
-                      const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, __nv_bfloat16* __restrict__ out) {
+dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kT,
+                      const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, __nv_bfloat16* out) {
   __shared__ float qs[DH];
   __shared__ __align__(16) float ps[XA_THREADS * 8];
   __shared__ float red[XA_THREADS / 8][DH];
   __shared__ float wred[2][XA_THREADS / 32];
   const int h = blockIdx.x, b = blockIdx.y, H = gridDim.x, tid = threadIdx.x;
   const long long bh = (long long)b * H + h;
+  pdl_launch_dependents();
+  pdl_wait();
   if (tid < DH) qs[tid] = __bfloat162float(q[(long long)b * d + h * DH + tid]) * (0.125f * 1.4426950408889634f);
   __syncthreads();
   // ---- scores for keys 8*tid .. 8*tid+7
@@ -245,6 +252,8 @@ constexpr int PICK_THREADS = 512;
 __global__ void __launch_bounds__(PICK_THREADS) dec_pick_kernel(const PickParams p) {
   __shared__ Stat sh[2][PICK_THREADS / 32];
   const int b = blockIdx.x, tid = threadIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
   const int pos = *p.pos;        // index of the token just consumed; we choose token pos+1
   const int nxt = pos + 1;
   if (nxt >= p.max_len) return;
@@ -332,7 +341,11 @@ __global__ void __launch_bounds__(PICK_THREADS) dec_pick_kernel(const PickParams
   }
 }
 
-__global__ void dec_advance_kernel(int32_t* pos) { *pos += 1; }
+__global__ void dec_advance_kernel(int32_t* pos) {
+  pdl_launch_dependents();
+  pdl_wait();
+  *pos += 1;
+}
 
 }  // namespace janus
 
@@ -342,9 +355,10 @@ using namespace janus;
 // dependency chain for K <= 1024; for more streams (or long K / the vocabulary projection) the
 // tcgen05 GEMM with 64-wide N tiles fills its 128-row MMA tiles and wins.
 static int linear(const __nv_bfloat16* A, int K, const void* W, const float* bias, const __nv_bfloat16* residual,
-                  void* out, int rows, int N, int act, int out_f32, cudaStream_t st) {
-  if (rows <= 64 && K <= 1024 && N <= 8192)
-    return dec_linear(A, K, static_cast<const __nv_bfloat16*>(W), bias, residual, out, rows, N, K, act, out_f32, st);
+                  void* out, int rows, int N, int act, int out_f32, cudaStream_t st, bool light = false) {
+  if (rows <= 64 && (light || (K <= 1024 && N <= 8192)))
+    return dec_linear(A, K, static_cast<const __nv_bfloat16*>(W), bias, residual, out, rows, N, K, act, out_f32, st,
+                      /*pdl=*/true);
   GemmParams q = {};
   q.M_per_batch = rows; q.n_batch = 1; q.N = N; q.K = K;
   q.out = static_cast<__nv_bfloat16*>(out); q.ldc = N; q.out_batch_stride = (long long)rows * N;
@@ -388,6 +402,10 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   JANUS_CHECK_ARG(c->n_ctx <= XA_THREADS * 8 && w->kv_ld % 8 == 0 && w->kv_ld >= c->n_ctx && w->kv_ld <= XA_THREADS * 8,
                   "decode_step: n_ctx=%d / kv_ld=%d unsupported", c->n_ctx, w->kv_ld);
   JANUS_CHECK_ARG(w->n_text_ctx <= 512, "decode_step: n_text_ctx must be <= 512");
+  const bool light = (s->flags & JANUS_DECODE_LIGHT) != 0;
+  const bool fused = (s->flags & JANUS_DECODE_FUSED) != 0;
+  JANUS_CHECK_ARG(!fused || s->barrier, "decode_step: JANUS_DECODE_FUSED needs state->barrier");
+  JANUS_CHECK_ARG(!light || s->batch <= 64, "decode_step: JANUS_DECODE_LIGHT needs batch <= 64 (got %d)", s->batch);
   cudaStream_t st = (cudaStream_t)stream_;
   const int B = s->batch, d = c->d, H = c->n_heads, T = c->n_ctx;
   __nv_bfloat16* x = static_cast<__nv_bfloat16*>(s->x);
@@ -397,43 +415,88 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   __nv_bfloat16* q = static_cast<__nv_bfloat16*>(s->q);
   __nv_bfloat16* ff = static_cast<__nv_bfloat16*>(s->ff);
   int rc;
-  dec_embed_kernel<<<B, 128, 0, st>>>(s->tokens, s->max_len, s->pos, static_cast<const __nv_bfloat16*>(w->tok_emb),
-                                      w->pos, d, x);
-  JANUS_LAUNCH_CHECK("dec_embed_kernel");
+  JANUS_CUDA(launch_pdl(dec_embed_kernel, dim3(B), dim3(128), 0, st, s->tokens, s->max_len, s->pos,
+                        static_cast<const __nv_bfloat16*>(w->tok_emb), w->pos, d, x));
   const long long self_stride = (long long)B * H * w->n_text_ctx * DH;
   const long long ck_stride = (long long)B * H * DH * w->kv_ld;
   const long long cv_stride = (long long)B * H * T * DH;
+  if (fused) {
+    FusedProgram base = {};
+    base.rows = B; base.d = d; base.n_heads = H; base.pos = s->pos;
+    base.barrier = reinterpret_cast<unsigned long long*>(s->barrier);
+    auto lin = [&](const void* A, int lda, const float* lw, const float* lb, const void* W, const float* bias,
+                   const void* res, void* out, int N, int K, int act, int cfg) {
+      FusedPhase ph = {};
+      ph.type = FZ_LINEAR;
+      ph.lin.A = A; ph.lin.lda = lda; ph.lin.ln_w = lw; ph.lin.ln_b = lb; ph.lin.W = W; ph.lin.bias = bias;
+      ph.lin.residual = res; ph.lin.out = out; ph.lin.N = N; ph.lin.K = K; ph.lin.kc = d; ph.lin.act = act;
+      ph.lin.cfg = cfg;
+      return ph;
+    };
+    auto tail_of = [&](FusedProgram& P, const janus_dec_layer_t& L) {   // ops after layer L's cross-attention
+      P.ph[P.n_phases++] = lin(att, d, nullptr, nullptr, L.w_co, L.b_co, x, x, d, d, ACT_NONE, 0);
+      P.ph[P.n_phases++] = lin(x, d, L.ln2_w, L.ln2_b, L.w_fc1, L.b_fc1, nullptr, ff, 4 * d, d, ACT_GELU, 2);
+      P.ph[P.n_phases++] = lin(ff, 4 * d, nullptr, nullptr, L.w_fc2, L.b_fc2, x, x, d, 4 * d, ACT_NONE, 0);
+    };
+    for (int l = 0; l < c->n_layers; ++l) {
+      const janus_dec_layer_t& L = w->layers[l];
+      FusedProgram P = base;
+      if (l > 0) tail_of(P, w->layers[l - 1]);
+      P.ph[P.n_phases++] = lin(x, d, L.ln1_w, L.ln1_b, L.w_qkv, L.b_qkv, nullptr, qkv, 3 * d, d, ACT_NONE, 1);
+      {
+        FusedPhase ph = {};
+        ph.type = FZ_SELF_ATTN;
+        ph.sa.qkv = qkv;
+        ph.sa.k_cache = static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride;
+        ph.sa.v_cache = static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride;
+        ph.sa.out = att; ph.sa.n_ctx = w->n_text_ctx;
+        P.ph[P.n_phases++] = ph;
+      }
+      P.ph[P.n_phases++] = lin(att, d, nullptr, nullptr, L.w_o, L.b_o, x, x, d, d, ACT_NONE, 0);
+      P.ph[P.n_phases++] = lin(x, d, L.lnc_w, L.lnc_b, L.w_cq, L.b_cq, nullptr, q, d, d, ACT_NONE, 0);
+      if ((rc = dec_fused_segment(P, st))) return rc;
+      JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(H, B), dim3(XA_THREADS), 0, st, q,
+                            static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
+                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att));
+    }
+    FusedProgram P = base;
+    tail_of(P, w->layers[c->n_layers - 1]);
+    {
+      FusedPhase ph = {};
+      ph.type = FZ_LAYERNORM;
+      ph.ln.x = x; ph.ln.w = w->ln_w; ph.ln.b = w->ln_b; ph.ln.y = xn;
+      P.ph[P.n_phases++] = ph;
+    }
+    if ((rc = dec_fused_segment(P, st))) return rc;
+  } else {
   for (int l = 0; l < c->n_layers; ++l) {
     const janus_dec_layer_t& L = w->layers[l];
-    if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st))) return rc;
-    dec_self_attn_kernel<<<dim3(H, B), 32, 0, st>>>(qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
-                                                    static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d,
-                                                    w->n_text_ctx, att);
-    JANUS_LAUNCH_CHECK("dec_self_attn_kernel");
-    if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st))) return rc;
-    if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st))) return rc;
-    dec_cross_attn_kernel<<<dim3(H, B), XA_THREADS, 0, st>>>(
-        q, static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-        static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att);
-    JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
-    if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st))) return rc;
-    if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st))) return rc;
-    if ((rc = linear(xn, d, L.w_fc1, L.b_fc1, nullptr, ff, B, 4 * d, ACT_GELU, 0, st))) return rc;
-    if ((rc = linear(ff, 4 * d, L.w_fc2, L.b_fc2, x, x, B, d, ACT_NONE, 0, st))) return rc;
+    if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
+    if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st, light))) return rc;
+    JANUS_CUDA(launch_pdl(dec_self_attn_kernel, dim3(H, B), dim3(32), 0, st, qkv,
+                          static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
+                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, w->n_text_ctx, att));
+    if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
+    if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
+    if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st, light))) return rc;
+    JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(H, B), dim3(XA_THREADS), 0, st, q,
+                          static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
+                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att));
+    if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
+    if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
+    if ((rc = linear(xn, d, L.w_fc1, L.b_fc1, nullptr, ff, B, 4 * d, ACT_GELU, 0, st, light))) return rc;
+    if ((rc = linear(ff, 4 * d, L.w_fc2, L.b_fc2, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
   }
-  if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st))) return rc;
-  if ((rc = linear(xn, d, w->tok_emb, nullptr, nullptr, s->logits, B, w->n_vocab_pad, ACT_NONE, 1, st))) return rc;
+  if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
+  }
+  if ((rc = linear(xn, d, w->tok_emb, nullptr, nullptr, s->logits, B, w->n_vocab_pad, ACT_NONE, 1, st, light))) return rc;
   PickParams pp;
   pp.logits = s->logits; pp.suppress = w->suppress_mask; pp.tokens = s->tokens; pp.forced = s->forced;
   pp.choice = s->choice; pp.logprob = s->logprob; pp.sum_logprob = s->sum_logprob; pp.pos = s->pos;
   pp.done = s->done; pp.n_done = s->n_done; pp.n_vocab = w->n_vocab; pp.n_vocab_pad = w->n_vocab_pad;
   pp.max_len = s->max_len; pp.n_prompt = s->n_prompt; pp.eot = w->eot; pp.blank = w->blank;
   pp.ts_begin = w->timestamp_begin; pp.max_initial_ts = w->max_initial_timestamp_index;
-  dec_pick_kernel<<<B, PICK_THREADS, 0, st>>>(pp);
-  JANUS_LAUNCH_CHECK("dec_pick_kernel");
-  dec_advance_kernel<<<1, 1, 0, st>>>(s->pos);
-  JANUS_LAUNCH_CHECK("dec_advance_kernel");
+  JANUS_CUDA(launch_pdl(dec_pick_kernel, dim3(B), dim3(PICK_THREADS), 0, st, pp));
+  JANUS_CUDA(launch_pdl(dec_advance_kernel, dim3(1), dim3(1), 0, st, s->pos));
   return JANUS_OK;
 }

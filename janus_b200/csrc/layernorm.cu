@@ -9,13 +9,17 @@ namespace janus {
 
 constexpr int LN_MAX_PAIRS = 20;  // d <= 1280 (large-v3)
 
-__global__ void __launch_bounds__(256) layernorm_bf16_kernel(const __nv_bfloat16* __restrict__ x,
+// x / y carry no __restrict__: under PDL (see common.cuh) x is written by the producer grid while this
+// grid is already resident, so it must not be read through the non-coherent path.
+__global__ void __launch_bounds__(256) layernorm_bf16_kernel(const __nv_bfloat16* x,
                                                              const float* __restrict__ w,
                                                              const float* __restrict__ b,
-                                                             __nv_bfloat16* __restrict__ y, long long rows, int d,
+                                                             __nv_bfloat16* y, long long rows, int d,
                                                              long long ldx, long long ldy) {
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
   if (row >= rows) return;
   const __nv_bfloat162* xr = reinterpret_cast<const __nv_bfloat162*>(x + row * ldx);
   const int npairs = d >> 6;  // bf16x2 pairs per lane
@@ -52,12 +56,17 @@ __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const __nv_bfloat16
 }
 
 int layernorm_bf16(const __nv_bfloat16* x, const float* w, const float* b, __nv_bfloat16* y, long long rows, int d,
-                   long long ldx, long long ldy, cudaStream_t stream) {
+                   long long ldx, long long ldy, cudaStream_t stream, bool pdl) {
   JANUS_CHECK_ARG(d % 64 == 0 && d <= 64 * LN_MAX_PAIRS, "layernorm: d=%d must be a multiple of 64 and <= %d", d,
                   64 * LN_MAX_PAIRS);
   if (rows <= 0) return JANUS_OK;
   const int wpb = 8;
-  layernorm_bf16_kernel<<<(unsigned)((rows + wpb - 1) / wpb), wpb * 32, 0, stream>>>(x, w, b, y, rows, d, ldx, ldy);
+  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
+  if (pdl) {
+    JANUS_CUDA(launch_pdl(layernorm_bf16_kernel, dim3(grid), dim3(wpb * 32), 0, stream, x, w, b, y, rows, d, ldx, ldy));
+    return JANUS_OK;
+  }
+  layernorm_bf16_kernel<<<grid, wpb * 32, 0, stream>>>(x, w, b, y, rows, d, ldx, ldy);
   JANUS_LAUNCH_CHECK("layernorm_bf16_kernel");
   return JANUS_OK;
 }
@@ -69,4 +78,16 @@ extern "C" int32_t janus_layernorm_bf16(const void* x, const float* w, const flo
   JANUS_CHECK_ARG(x && w && b && y, "layernorm: null pointer");
   return janus::layernorm_bf16(static_cast<const __nv_bfloat16*>(x), w, b, static_cast<__nv_bfloat16*>(y), rows, d, d,
                                d, (cudaStream_t)stream);
+}
+
+// Diagnostic (not part of the product path): n dependent LayerNorm launches issued from C, for measuring
+// the dependent-launch latency of the decode chain with and without PDL (scripts/gpu_dec_bench2.py).
+extern "C" int32_t janus_debug_ln_chain(const void* x, const float* w, const float* b, void* y, int64_t rows,
+                                        int32_t d, int32_t n, void* stream) {
+  for (int i = 0; i < n; ++i) {
+    int rc = janus::layernorm_bf16(static_cast<const __nv_bfloat16*>(x), w, b, static_cast<__nv_bfloat16*>(y), rows, d,
+                                   d, d, (cudaStream_t)stream, true);
+    if (rc) return rc;
+  }
+  return JANUS_OK;
 }

@@ -52,76 +52,183 @@ def join_segments(segs: list[str]) -> str:
 
 @dataclass
 class EncodeResult:
+    """Device-side results of one `encode_device` call. The work is still in flight on the lane
+    streams when this is returned: call `wait()` (stream-side join) or `synchronize()` before reading.
+    The tensors are slots of a small ring and stay valid for `SemanticEncoder.result_slots - 1`
+    further calls."""
     tokens: torch.Tensor        # int32 [B, max_new] (device)
     sum_logprob: torch.Tensor   # fp32 [B]
     tags: torch.Tensor          # uint8 [B, 2] (device)
+    events: list                # one per lane: recorded after the lane wrote its rows
+
+    def wait(self, stream: torch.cuda.Stream | None = None) -> "EncodeResult":
+        st = stream if stream is not None else torch.cuda.current_stream(self.tokens.device)
+        for ev in self.events:
+            st.wait_event(ev)
+        return self
+
+    def synchronize(self) -> "EncodeResult":
+        for ev in self.events:
+            ev.synchronize()
+        return self
+
+
+class _Lane:
+    """One decode lane: `lane_batch` windows with their own KV caches, CUDA graph and stream."""
+
+    def __init__(self, enc: "SemanticEncoder", index: int) -> None:
+        dev = enc.device
+        self.index = index
+        self.stream = torch.cuda.Stream(dev)
+        with torch.cuda.stream(self.stream):
+            self.session = DecodeSession(enc.whisper, enc.lane_batch, enc.max_new_tokens, light=enc.light,
+                                         steps_per_graph=enc.steps_per_graph)
+            self.session._ensure_graph()
+        self.stream.synchronize()
+        self.ready = torch.cuda.Event()    # encoder stream -> lane: cross-KV of this lane is written
+        self.free = torch.cuda.Event()     # lane -> encoder stream: the lane finished decoding
+        self.free.record(self.stream)
+        self.pros_out: dict = {}
 
 
 class SemanticEncoder:
-    """Fixed-batch engine: B windows of up to 30 s each, one launch sequence per step."""
+    """Batched engine for one GPU. A call encodes `batch` windows (each up to 30 s) as
+    `batch / lane_batch` *lanes*:
+
+      encoder stream   for each lane in turn: YIN/RMS prosody, log-mel, Whisper encoder (tensor-pipe
+                       bound, tcgen05) and the cross-K/V projection of that lane's windows
+      lane streams     the lane's greedy decode (HBM-bound: 55 MB of cross-K/V per window and step),
+                       replayed from a CUDA graph, then a copy of its tokens/tags into the result slot
+
+    The decode kernels of a lane use no TMEM and < 32 KB of shared memory (JANUS_DECODE_LIGHT), so they
+    share the SMs with the persistent tcgen05 GEMM / attention CTAs of the encoder stream: the HBM-bound
+    decode of earlier lanes overlaps the tensor-bound encoder of later lanes -- also across calls, since
+    there are `n_lanes` >= 2 * batch / lane_batch lanes used round-robin and a call only enqueues work.
+    """
 
     def __init__(self, model: str | WhisperDims = "small", batch: int = 64, max_new_tokens: int = 128,
                  device=None, seed: int = 0, weights: dict | None = None, weight_profile: str = "confident",
-                 prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, enc_chunk: int = 64) -> None:
+                 prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, lane_batch: int = 64,
+                 n_lanes: int | None = None, steps_per_graph: int = 10, light: bool | None = None) -> None:
         self.dims = PRESETS[model] if isinstance(model, str) else model
         self.spec = tokenizer_spec(self.dims)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         if weights is None:  # no checkpoints exist offline: random init of the named architecture
             weights = init_random_weights(self.dims, seed=seed, profile=weight_profile)
-        self.whisper = WhisperEngine(self.dims, weights, self.device, self.spec)
-        self.session = DecodeSession(self.whisper, batch, max_new_tokens)
-        self.prosody = ProsodyEngine(self.device, sample_rate=prosody_sample_rate)
         self.batch = batch
+        self.lane_batch = min(lane_batch, batch)
+        if batch % self.lane_batch:
+            raise ValueError(f"batch {batch} must be a multiple of lane_batch {self.lane_batch}")
+        self.lanes_per_call = batch // self.lane_batch
+        self.n_lanes = n_lanes if n_lanes is not None else 2 * self.lanes_per_call
+        if self.n_lanes < self.lanes_per_call:
+            raise ValueError("n_lanes must be >= batch / lane_batch")
+        self.light = (self.lane_batch <= 64) if light is None else light
+        self.max_new_tokens, self.steps_per_graph = max_new_tokens, steps_per_graph
         self.decim = input_sample_rate // 16000
         assert input_sample_rate in (16000, 48000)
-        self._plans: dict = {}
         d = self.dims
-        # the encoder is compute-bound and runs in micro-batches of `enc_chunk` windows (bounded workspace);
-        # the decoder is latency/memory-bound and steps all `batch` windows at once so its per-step fixed
-        # costs are amortised over as many streams as fit
-        self.enc_chunk = min(enc_chunk, batch)
-        self.mel_pad = torch.empty((self.enc_chunk, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16,
-                                   device=self.device)
-        self.mel_scratch = torch.empty((self.enc_chunk, self.whisper.frontend.frames_alloc, d.n_mels),
-                                       dtype=torch.float32, device=self.device)
-        self.enc_out = torch.empty((batch, d.n_audio_ctx, d.n_audio_state), dtype=torch.bfloat16, device=self.device)
-        self._pros_out = None
+        with torch.cuda.device(self.device):
+            self.whisper = WhisperEngine(self.dims, weights, self.device, self.spec)
+            self.prosody = ProsodyEngine(self.device, sample_rate=prosody_sample_rate)
+            # high priority: when an SM frees up, the (few, large, persistent) tcgen05 CTAs of the encoder are
+            # placed before the many small decode CTAs, which then fill the remaining threads / shared memory
+            self.enc_stream = torch.cuda.Stream(self.device, priority=-1)
+            self.lanes = [_Lane(self, i) for i in range(self.n_lanes)]
+            self._next_lane = 0
+            lb = self.lane_batch
+            # encoder-stream buffers, shared by all lanes (the encoder stream is in-order)
+            self.mel_pad = torch.empty((lb, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16, device=self.device)
+            self.mel_scratch = torch.empty((lb, self.whisper.frontend.frames_alloc, d.n_mels), dtype=torch.float32,
+                                           device=self.device)
+            self.enc_out = torch.empty((lb, d.n_audio_ctx, d.n_audio_state), dtype=torch.bfloat16, device=self.device)
+            self.max_new = self.lanes[0].session.max_new
+            self.result_slots = -(-self.n_lanes // self.lanes_per_call) + 1
+            self._results = [(torch.zeros((batch, self.max_new), dtype=torch.int32, device=self.device),
+                              torch.zeros(batch, dtype=torch.float32, device=self.device),
+                              torch.zeros((batch, 2), dtype=torch.uint8, device=self.device))
+                             for _ in range(self.result_slots)]
+            self._slot = 0
+        self._plans: dict = {}
+        self.session = self.lanes[0].session   # (single-lane callers / diagnostics)
 
-    def _plan(self, lengths: tuple):
+    # ---- planning -------------------------------------------------------------------------
+    def _lane_plan(self, lengths: tuple):
+        """Index arrays for one lane's windows (offsets relative to the lane's first sample)."""
         p = self._plans.get(lengths)
         if p is None:
             plan = self.prosody.plan(list(lengths))
             offs = torch.from_numpy(plan.offsets).to(self.device)
             lens = torch.from_numpy(plan.lengths).to(self.device)
-            p = (plan, offs, lens, self.prosody.alloc_outputs(plan))
+            p = (plan, offs, lens)
             self._plans[lengths] = p
         return p
 
     def kernels_per_step(self) -> int:
-        n_chunks = -(-self.batch // self.enc_chunk)
-        enc = n_chunks * (2 + 7 * self.dims.n_audio_layer + 1 + 2)  # stem, layers, ln_post, 2 logmel kernels
-        dec = 1 + self.session.n_steps * self.session.kernels_per_step
-        return enc + dec + 2
+        enc = self.lanes_per_call * (2 + 2 + 2 + 7 * self.dims.n_audio_layer + 1 + 1)  # prosody, log-mel, stem, layers, ln_post, cross-KV
+        ses = self.lanes[0].session
+        return enc + self.lanes_per_call * ses.n_steps * ses.kernels_per_step
 
-    def encode_device(self, pcm: torch.Tensor, lengths: tuple) -> EncodeResult:
-        """pcm: float32 device tensor, the B windows concatenated (source-rate samples); lengths: per
-        window sample counts. Asynchronous on the current stream."""
+    # ---- the path -------------------------------------------------------------------------
+    def encode_lane_front(self, lane: _Lane, pcm: torch.Tensor, lengths: tuple) -> None:
+        """Prosody + K1 + K2 + cross-K/V of one lane's windows; call under the encoder stream."""
+        plan, offs, lens = self._lane_plan(lengths)
+        out = lane.pros_out.get(lengths)
+        if out is None:
+            out = lane.pros_out[lengths] = self.prosody.alloc_outputs(plan)
+        lane.cur_pros = out
+        self.prosody.run(pcm, plan, out=out)
+        self.whisper.frontend(pcm, offs, lens, decim=self.decim, scratch=self.mel_scratch, out_bf16=self.mel_pad)
+        self.whisper.encode(self.mel_pad, out=self.enc_out)
+        lane.session.cross_kv(self.enc_out)
+
+    def encode_device(self, pcm: torch.Tensor, lengths, host_pcm: torch.Tensor | None = None) -> EncodeResult:
+        """pcm: float32 device tensor holding the `batch` windows concatenated (source-rate samples);
+        lengths: per-window sample counts. If `host_pcm` (pinned) is given, each lane's slice is first
+        copied host->device into `pcm` on the encoder stream. Only enqueues work; see EncodeResult."""
+        lengths = tuple(int(v) for v in lengths)
         assert len(lengths) == self.batch
-        plan, offs, lens, pros_out = self._plan(tuple(lengths))
-        self.prosody.run(pcm, plan, out=pros_out)
-        self.encode_windows(pcm, offs, lens)
-        tokens, sum_lp = self.session.decode(self.enc_out)
-        return EncodeResult(tokens, sum_lp, pros_out["tags"])
+        lb = self.lane_batch
+        dev = self.device
+        tokens, sum_lp, tags = self._results[self._slot]
+        self._slot = (self._slot + 1) % self.result_slots
+        cur = torch.cuda.current_stream(dev)
+        ev_in = torch.cuda.Event()
+        ev_in.record(cur)
+        self.enc_stream.wait_event(ev_in)
+        events = []
+        start = 0
+        for j in range(self.lanes_per_call):
+            lane = self.lanes[self._next_lane]
+            self._next_lane = (self._next_lane + 1) % self.n_lanes
+            ll = lengths[j * lb:(j + 1) * lb]
+            n = sum(ll)
+            sl = pcm[start:start + n]
+            with torch.cuda.stream(self.enc_stream):
+                self.enc_stream.wait_event(lane.free)
+                if host_pcm is not None:
+                    sl.copy_(host_pcm[start:start + n], non_blocking=True)
+                self.encode_lane_front(lane, sl, ll)
+                lane.ready.record(self.enc_stream)
+            with torch.cuda.stream(lane.stream):
+                lane.stream.wait_event(lane.ready)
+                ses = lane.session
+                ses.reset()
+                ses.run_steps()
+                r = slice(j * lb, (j + 1) * lb)
+                tokens[r].copy_(ses.tokens[:, ses.n_prompt:], non_blocking=True)
+                sum_lp[r].copy_(ses.sum_logprob, non_blocking=True)
+                tags[r].copy_(lane.cur_pros["tags"], non_blocking=True)
+                lane.free = torch.cuda.Event()
+                lane.free.record(lane.stream)
+                events.append(lane.free)
+            start += n
+        return EncodeResult(tokens, sum_lp, tags, events)
 
-    def encode_windows(self, pcm: torch.Tensor, offs: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
-        """K1 + K2 over all windows in micro-batches; fills self.enc_out [batch, n_ctx, d]."""
-        for c0 in range(0, self.batch, self.enc_chunk):
-            c1 = min(c0 + self.enc_chunk, self.batch)
-            n = c1 - c0
-            self.whisper.frontend(pcm, offs[c0:c1], lens[c0:c1], decim=self.decim, scratch=self.mel_scratch[:n],
-                                  out_bf16=self.mel_pad[:n])
-            self.whisper.encode(self.mel_pad[:n], out=self.enc_out[c0:c1])
-        return self.enc_out
+    def synchronize(self) -> None:
+        self.enc_stream.synchronize()
+        for lane in self.lanes:
+            lane.stream.synchronize()
 
     def to_packets(self, tokens_host: np.ndarray, tags_host: np.ndarray, timestamps=None,
                    mode: JanusMode = JanusMode.SEMANTIC_VOICE, override_emotion=None):
@@ -131,15 +238,16 @@ class SemanticEncoder:
 
     def encode_host(self, buffers: list[np.ndarray], timestamps=None):
         """Host buffers in, packets out (H2D + kernels + D2H + MessagePack). Synchronises."""
+        assert len(buffers) == self.batch
         lengths = tuple(len(b) for b in buffers)
-        host = torch.empty(sum(lengths), dtype=torch.float32, pin_memory=True)
+        host = torch.empty(max(sum(lengths), 1), dtype=torch.float32, pin_memory=True)
         hv, o = host.numpy(), 0
         for b in buffers:
             hv[o:o + len(b)] = b
             o += len(b)
         with torch.cuda.device(self.device):
-            pcm = host.to(self.device, non_blocking=True)
-            res = self.encode_device(pcm, lengths)
+            pcm = torch.empty(host.numel(), dtype=torch.float32, device=self.device)
+            res = self.encode_device(pcm, lengths, host_pcm=host).wait()
             tok = res.tokens.cpu().numpy()
             tags = res.tags.cpu().numpy()
         return self.to_packets(tok, tags, timestamps)

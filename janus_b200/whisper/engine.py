@@ -123,10 +123,10 @@ class DecWeightsStruct(C.Structure):
 
 
 class DecodeStateStruct(C.Structure):
-    _fields_ = [("batch", C.c_int32), ("max_len", C.c_int32), ("n_prompt", C.c_int32)] + \
+    _fields_ = [("batch", C.c_int32), ("max_len", C.c_int32), ("n_prompt", C.c_int32), ("flags", C.c_int32)] + \
                [(n, C.c_void_p) for n in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done",
                                           "n_done", "self_k", "self_v", "cross_k", "cross_v", "x", "xn", "qkv",
-                                          "att", "q", "ff", "logits")]
+                                          "att", "q", "ff", "logits", "barrier")]
 
 
 def _pack_decoder(self, W) -> None:
@@ -178,7 +178,11 @@ WhisperEngine._pack_decoder = _pack_decoder
 class DecodeSession:
     """Greedy decode of a fixed-size batch: owns the KV caches and the captured CUDA graph of one step."""
 
-    def __init__(self, engine: WhisperEngine, batch: int, max_new_tokens: int, use_graph: bool = True) -> None:
+    DECODE_LIGHT = 1   # JANUS_DECODE_LIGHT
+    DECODE_FUSED = 2   # JANUS_DECODE_FUSED
+
+    def __init__(self, engine: WhisperEngine, batch: int, max_new_tokens: int, use_graph: bool = True,
+                 light: bool = False, steps_per_graph: int = 1, fused: bool = False) -> None:
         if not hasattr(engine, "dec_weights"):
             raise RuntimeError("engine was built without decoder weights")
         self.eng, self.B = engine, batch
@@ -209,6 +213,12 @@ class DecodeSession:
         self.prompt = torch.tensor(list(spec.sot_sequence), **i32)
         s = DecodeStateStruct()
         s.batch, s.max_len, s.n_prompt = B, self.max_len, self.n_prompt
+        if light and B > 64:
+            raise ValueError("light decode sessions hold at most 64 streams")
+        s.flags = (self.DECODE_LIGHT if light else 0) | (self.DECODE_FUSED if fused else 0)
+        self.barrier = torch.zeros(2, dtype=torch.int64, device=dev)   # grid-barrier counter of the fused path
+        s.barrier = self.barrier.data_ptr()
+        self.fused = fused
         for name in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done", "n_done", "self_k",
                      "self_v", "cross_k", "cross_v", "x", "xn", "qkv", "att", "q", "ff", "logits"):
             setattr(s, name, getattr(self, name).data_ptr())
@@ -216,7 +226,12 @@ class DecodeSession:
         self.use_graph = use_graph
         self.graph: torch.cuda.CUDAGraph | None = None
         self.n_steps = self.n_prompt + self.max_new - 1
-        self.kernels_per_step = 3 + 11 * L + 2 + 1  # embed, final LN, logits, pick, advance + 11 per layer
+        # several steps per captured graph: fewer host launches per lane when many lanes are in flight
+        self.steps_per_graph = max(1, min(steps_per_graph, self.n_steps))
+        self.tail_graph: torch.cuda.CUDAGraph | None = None
+        # embed, final LN, logits, pick, advance + 11 per layer; fused: embed, (segment + cross-attn) per layer,
+        # final segment, logits, pick, advance
+        self.kernels_per_step = (1 + 2 * L + 1 + 3) if fused else (3 + 11 * L + 2 + 1)
 
     def _step(self) -> None:
         e = self.eng
@@ -251,17 +266,38 @@ class DecodeSession:
         torch.cuda.current_stream(self.eng.device).synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            self._step()
+            for _ in range(self.steps_per_graph):
+                self._step()
         self.graph = g
+        rem = self.n_steps % self.steps_per_graph
+        if rem:
+            t = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(t):
+                for _ in range(rem):
+                    self._step()
+            self.tail_graph = t
+
+    def run_steps(self, n_steps: int | None = None) -> None:
+        """Enqueues n_steps decode steps (default: all) on the current stream."""
+        n = self.n_steps if n_steps is None else n_steps
+        if self.graph is None:
+            for _ in range(n):
+                self._step()
+            return
+        full, rem = divmod(n, self.steps_per_graph)
+        for _ in range(full):
+            self.graph.replay()
+        if rem:
+            if rem == self.n_steps % self.steps_per_graph and self.tail_graph is not None:
+                self.tail_graph.replay()
+            else:
+                for _ in range(rem):
+                    self._step()
 
     def decode(self, enc_out: torch.Tensor, forced: torch.Tensor | None = None, n_steps: int | None = None):
         """Returns (tokens [B, max_new] int32 device, sum_logprob [B]). Does not synchronise."""
         self._ensure_graph()
         self.cross_kv(enc_out)
         self.reset(forced)
-        for _ in range(self.n_steps if n_steps is None else n_steps):
-            if self.graph is not None:
-                self.graph.replay()
-            else:
-                self._step()
+        self.run_steps(n_steps)
         return self.tokens[:, self.n_prompt:], self.sum_logprob

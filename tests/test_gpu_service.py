@@ -70,3 +70,35 @@ def test_semantic_encoder_packets_match_oracle():
         assert texts[i] == ref_text, i
         ref_pkt = JanusPacket(ref_text, JanusMode.SEMANTIC_VOICE, tags, None, ts[i]).serialize()
         assert pkts[i] == ref_pkt, i
+
+
+def test_semantic_encoder_lanes_pipelined_calls_are_bit_identical():
+    """4 windows as 2 lanes of 2 (4 lanes round-robin), three calls enqueued back to back without a
+    host sync: every call returns the tokens/tags of a single-lane engine, bit for bit."""
+    import torch
+    from janus_b200.pipeline import SemanticEncoder
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import test_dims
+    from janus_b200.whisper.weights import init_random_weights
+    dims = test_dims(d=128, heads=2, layers=2)
+    W = init_random_weights(dims, seed=3, profile="confident")
+    B, n_new = 4, 24
+    clips = make_clips(2 * B, 30.0, 16000, seed=5, device="cuda")
+    lens = (480000, 200000, 480000, 90001)
+    def pack(c):
+        return torch.cat([c[i, :lens[i]] for i in range(B)]).contiguous()
+    xa, xb = pack(clips[:B]), pack(clips[B:])
+    one = SemanticEncoder(dims, batch=B, max_new_tokens=n_new, weights=W, lane_batch=B, n_lanes=1, steps_per_graph=1)
+    ra = one.encode_device(xa, lens).synchronize()
+    ta, ga = ra.tokens.clone(), ra.tags.clone()
+    rb = one.encode_device(xb, lens).synchronize()
+    tb, gb = rb.tokens.clone(), rb.tags.clone()
+    assert not torch.equal(ta, tb)
+    multi = SemanticEncoder(dims, batch=B, max_new_tokens=n_new, weights=W, lane_batch=2, n_lanes=4, steps_per_graph=7)
+    r1 = multi.encode_device(xa, lens)
+    r2 = multi.encode_device(xb, lens)
+    r3 = multi.encode_device(xa, lens)
+    multi.synchronize()
+    assert torch.equal(r1.tokens, ta) and torch.equal(r1.tags, ga)
+    assert torch.equal(r2.tokens, tb) and torch.equal(r2.tags, gb)
+    assert torch.equal(r3.tokens, ta) and torch.equal(r3.tags, ga)
