@@ -329,12 +329,13 @@ def main() -> None:
                     help="stt_prosody = the headline metric (Whisper STT + prosody -> packets); "
                          "prosody = BASELINE configs[1] alone")
     ap.add_argument("--model", default="small")
-    ap.add_argument("--batch", type=int, default=256,
+    ap.add_argument("--batch", type=int, default=1024,
                     help="30 s windows per GPU per step (stt_prosody): encoder micro-batches of 64 (configs[2]), "
-                         "decoder steps all of them together")
-    ap.add_argument("--lane-batch", type=int, default=64, help="windows per decode lane (stt_prosody)")
+                         "decoder steps a whole lane of them together")
+    ap.add_argument("--lane-batch", type=int, default=1024, help="windows per decode lane (stt_prosody)")
     ap.add_argument("--lanes", type=int, default=0, help="decode lanes in flight (0 = 2 x batch / lane_batch)")
     ap.add_argument("--steps-per-graph", type=int, default=10)
+    ap.add_argument("--fused", action="store_true", help="fused persistent segment kernel instead of per-op decode kernels")
     ap.add_argument("--max-new-tokens", type=int, default=128)
     ap.add_argument("--streams", type=int, default=4096, help="streams per GPU (prosody workload)")
     ap.add_argument("--clip-seconds", type=float, default=30.0)

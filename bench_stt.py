@@ -23,7 +23,8 @@ def stt_config(args, batch: int) -> dict:
                     "cross-KV) runs lane by lane while earlier lanes decode on their own streams; calls are enqueued "
                     "back to back and fully drained inside the timed region",
         "parallelism": f"dp{args.gpus} over independent windows, no collective",
-        "l2": "per-step working set (cross-KV 3.5 GB + activations) is far larger than the 126 MB L2",
+        "encoder_micro_batch": 64,
+        "l2": "per-step working set (cross-KV 56 MB per window + activations) is far larger than the 126 MB L2",
     }
 
 
@@ -127,7 +128,8 @@ def run_gpu_stt(args) -> None:
 
     enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
                           prosody_sample_rate=sr, input_sample_rate=sr, lane_batch=args.lane_batch,
-                          n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph)
+                          n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph,
+                          fused=args.fused)
     N = int(round(seconds * sr))
     x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)
     lengths = tuple([N] * B)
@@ -172,9 +174,7 @@ def run_gpu_stt(args) -> None:
         enc.prosody.run(x[j * lb * N:(j + 1) * lb * N], plan, out=enc.lanes[j].pros_out[ll])
     ev[1].record()
     for j in range(enc.lanes_per_call):
-        enc.whisper.frontend(x[j * lb * N:(j + 1) * lb * N], offs, lens, decim=enc.decim, scratch=enc.mel_scratch,
-                             out_bf16=enc.mel_pad)
-        enc.whisper.encode(enc.mel_pad, out=enc.enc_out)
+        enc.encode_lane_windows(x[j * lb * N:(j + 1) * lb * N], offs, lens)
     ev[2].record()
     for j in range(enc.lanes_per_call):
         enc.lanes[j].session.cross_kv(enc.enc_out)

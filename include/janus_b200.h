@@ -107,6 +107,10 @@ int32_t janus_layernorm_bf16(const void* x, const float* w, const float* b, void
 /* Diagnostic: n dependent LayerNorm launches (PDL chain) issued from C; used to measure launch latency. */
 int32_t janus_debug_ln_chain(const void* x, const float* w, const float* b, void* y, int64_t rows, int32_t d,
                              int32_t n, void* stream);
+/* Diagnostic: a fused decode segment of n_phases identical linear phases (timing of one phase + grid barrier). */
+int32_t janus_debug_fused_linear(const void* A, const void* W, const float* bias, void* out, const float* ln_w,
+                                 const float* ln_b, int32_t rows, int32_t N, int32_t K, int32_t d, int32_t cfg,
+                                 int32_t n_phases, void* barrier, const int32_t* pos, void* stream);
 int32_t janus_attention_enc_bf16(const void* qkv, void* out, int32_t n_batch, int32_t T, int32_t n_heads,
                                  void* stream);
 
@@ -197,6 +201,9 @@ typedef struct {
 typedef struct {
   int32_t batch, max_len, n_prompt;    /* max_len = n_prompt + max_new_tokens */
   int32_t flags;                       /* JANUS_DECODE_* */
+  int32_t self_ld;                     /* positions allocated per (stream, head) in self_k / self_v; 0 = n_text_ctx.
+                                          Must be >= max_len (a session that decodes 131 tokens need not hold 448) */
+  int32_t reserved0;
   int32_t* tokens;                     /* [batch, max_len]; the sot prompt is pre-filled by the caller */
   const int32_t* forced;               /* [batch, max_len] teacher forcing (-1 = free) or NULL */
   int32_t* choice;                     /* [batch, max_len] argmax under the rules (diagnostic) or NULL */
@@ -205,7 +212,7 @@ typedef struct {
   int32_t* pos;                        /* device scalar: index of the token the next step consumes */
   uint8_t* done;                       /* [batch] */
   int32_t* n_done;                     /* device scalar */
-  void* self_k; void* self_v;          /* bf16 [L, batch, H, n_text_ctx, 64] */
+  void* self_k; void* self_v;          /* bf16 [L, batch, H, self_ld, 64] */
   const void* cross_k;                 /* bf16 [L, batch, H, 64, kv_ld]  (keys contiguous) */
   const void* cross_v;                 /* bf16 [L, batch, H, n_ctx, 64] */
   void* x; void* xn; void* qkv; void* att; void* q; void* ff;  /* bf16 [batch, d|d|3d|d|d|4d] */

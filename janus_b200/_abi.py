@@ -32,6 +32,7 @@ SIGNATURES = {
     "janus_prosody_reduce_f32": (_I32, [_P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P]),
     "janus_layernorm_bf16": (_I32, [_P, _P, _P, _P, _I64, _I32, _P]),
     "janus_debug_ln_chain": (_I32, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),
+    "janus_debug_fused_linear": (_I32, [_P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _I32, _P, _P, _P]),
     "janus_attention_enc_bf16": (_I32, [_P, _P, _I32, _I32, _I32, _P]),
     "janus_logmel_frames_alloc": (_I32, []),
     "janus_logmel_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _P, _P, _P, _P]),

@@ -409,3 +409,23 @@ int dec_fused_segment(const FusedProgram& prog, cudaStream_t stream) {
 }
 
 }  // namespace janus
+
+// Diagnostic (not on the product path): a segment of `n_phases` identical linear phases, for timing one
+// phase + barrier in isolation (scripts/gpu_fused_probe.py).
+extern "C" int32_t janus_debug_fused_linear(const void* A, const void* W, const float* bias, void* out,
+                                            const float* ln_w, const float* ln_b, int32_t rows, int32_t N, int32_t K,
+                                            int32_t d, int32_t cfg, int32_t n_phases, void* barrier, const int32_t* pos,
+                                            void* stream) {
+  using namespace janus;
+  FusedProgram P = {};
+  P.rows = rows; P.d = d; P.n_heads = d / 64; P.pos = pos;
+  P.barrier = static_cast<unsigned long long*>(barrier);
+  for (int i = 0; i < n_phases && i < FZ_MAX_PHASES; ++i) {
+    FusedPhase ph = {};
+    ph.type = FZ_LINEAR;
+    ph.lin.A = A; ph.lin.lda = K; ph.lin.ln_w = ln_w; ph.lin.ln_b = ln_b; ph.lin.W = W; ph.lin.bias = bias;
+    ph.lin.out = out; ph.lin.N = N; ph.lin.K = K; ph.lin.kc = d; ph.lin.cfg = cfg;
+    P.ph[P.n_phases++] = ph;
+  }
+  return dec_fused_segment(P, (cudaStream_t)stream);
+}

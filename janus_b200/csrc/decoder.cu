@@ -17,6 +17,8 @@
 // rule filter + log-softmax + argmax run in one pass of one CTA per stream.
 // All per-step scalars (position, done flags) live in device memory so the whole step is one
 // CUDA graph that the host replays.
+#include <stdlib.h>
+
 #include "kernels.cuh"
 
 namespace janus {
@@ -111,15 +113,20 @@ constexpr int XA_THREADS = 192;  // 192 * 8 keys = 1536 >= 1500
 
 __global__ void __launch_bounds__(XA_THREADS)
 dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kT,
-                      const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, __nv_bfloat16* out) {
+                      const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, int H, int n_items,
+                      __nv_bfloat16* out) {
+  // 6.4 KB of shared memory and 40 registers per thread: with the grid capped at 3 CTAs per SM (xa_grid)
+  // three of these fit beside one persistent tcgen05 GEMM CTA of the encoder stream (198 KB, 41 K registers)
   __shared__ float qs[DH];
   __shared__ __align__(16) float ps[XA_THREADS * 8];
-  __shared__ float red[XA_THREADS / 8][DH];
   __shared__ float wred[2][XA_THREADS / 32];
-  const int h = blockIdx.x, b = blockIdx.y, H = gridDim.x, tid = threadIdx.x;
-  const long long bh = (long long)b * H + h;
+  float (*red)[DH] = reinterpret_cast<float (*)[DH]>(ps);   // [XA_THREADS / 8][DH], reuses ps after the PV pass
+  const int tid = threadIdx.x;
   pdl_launch_dependents();
   pdl_wait();
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+  const int b = item / H, h = item - b * H;
+  const long long bh = (long long)b * H + h;
   if (tid < DH) qs[tid] = __bfloat162float(q[(long long)b * d + h * DH + tid]) * (0.125f * 1.4426950408889634f);
   __syncthreads();
   // ---- scores for keys 8*tid .. 8*tid+7
@@ -186,6 +193,7 @@ dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ 
       o[2 * e + 1] = fmaf(p, f.y, o[2 * e + 1]);
     }
   }
+  __syncthreads();   // every thread is done reading ps: reuse it for the cross-row reduction
 #pragma unroll
   for (int i = 0; i < 8; ++i) red[rg][c * 8 + i] = o[i];
   __syncthreads();
@@ -195,6 +203,20 @@ dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ 
     for (int r = 0; r < XA_THREADS / 8; ++r) t += red[r][tid];
     out[(long long)b * d + h * DH + tid] = __float2bfloat16_rn(t / sum);
   }
+  }  // item loop (the next iteration's first __syncthreads orders the reuse of qs / ps)
+}
+
+// Grid of the cross-attention kernel: one CTA per (stream, head) by default; JANUS_XA_CTAS_PER_SM=n makes it
+// persistent with n CTAs per SM so that tcgen05 CTAs of a concurrent encoder stream always find room.
+static int xa_grid(int n_items) {
+  static int cap = -1;
+  if (cap < 0) {
+    const char* e = getenv("JANUS_XA_CTAS_PER_SM");
+    cap = e ? atoi(e) : 0;
+  }
+  if (cap <= 0) return n_items;
+  const long long g = (long long)cap * num_sms();
+  return n_items < g ? n_items : (int)g;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -373,9 +395,10 @@ extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k,
   JANUS_CHECK_ARG(q && cross_k && cross_v && out && batch > 0 && n_heads > 0, "cross_attn: bad argument");
   JANUS_CHECK_ARG(n_ctx <= XA_THREADS * 8 && kv_ld % 8 == 0 && kv_ld >= n_ctx && kv_ld <= XA_THREADS * 8,
                   "cross_attn: n_ctx=%d / kv_ld=%d unsupported", n_ctx, kv_ld);
-  dec_cross_attn_kernel<<<dim3(n_heads, batch), XA_THREADS, 0, (cudaStream_t)stream>>>(
+  dec_cross_attn_kernel<<<xa_grid(n_heads * batch), XA_THREADS, 0, (cudaStream_t)stream>>>(
       static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(cross_k),
-      static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, static_cast<__nv_bfloat16*>(out));
+      static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, n_heads, n_heads * batch,
+      static_cast<__nv_bfloat16*>(out));
   JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
   return JANUS_OK;
 }
@@ -417,7 +440,10 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   int rc;
   JANUS_CUDA(launch_pdl(dec_embed_kernel, dim3(B), dim3(128), 0, st, s->tokens, s->max_len, s->pos,
                         static_cast<const __nv_bfloat16*>(w->tok_emb), w->pos, d, x));
-  const long long self_stride = (long long)B * H * w->n_text_ctx * DH;
+  const int self_ld = s->self_ld > 0 ? s->self_ld : w->n_text_ctx;
+  JANUS_CHECK_ARG(self_ld >= s->max_len && self_ld <= 512, "decode_step: self_ld=%d must be in [max_len=%d, 512]", self_ld,
+                  s->max_len);
+  const long long self_stride = (long long)B * H * self_ld * DH;
   const long long ck_stride = (long long)B * H * DH * w->kv_ld;
   const long long cv_stride = (long long)B * H * T * DH;
   if (fused) {
@@ -449,15 +475,15 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
         ph.sa.qkv = qkv;
         ph.sa.k_cache = static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride;
         ph.sa.v_cache = static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride;
-        ph.sa.out = att; ph.sa.n_ctx = w->n_text_ctx;
+        ph.sa.out = att; ph.sa.n_ctx = self_ld;
         P.ph[P.n_phases++] = ph;
       }
       P.ph[P.n_phases++] = lin(att, d, nullptr, nullptr, L.w_o, L.b_o, x, x, d, d, ACT_NONE, 0);
       P.ph[P.n_phases++] = lin(x, d, L.lnc_w, L.lnc_b, L.w_cq, L.b_cq, nullptr, q, d, d, ACT_NONE, 0);
       if ((rc = dec_fused_segment(P, st))) return rc;
-      JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(H, B), dim3(XA_THREADS), 0, st, q,
+      JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                             static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att));
+                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
     }
     FusedProgram P = base;
     tail_of(P, w->layers[c->n_layers - 1]);
@@ -475,13 +501,13 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
     if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st, light))) return rc;
     JANUS_CUDA(launch_pdl(dec_self_attn_kernel, dim3(H, B), dim3(32), 0, st, qkv,
                           static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
-                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, w->n_text_ctx, att));
+                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, att));
     if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st, light))) return rc;
-    JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(H, B), dim3(XA_THREADS), 0, st, q,
+    JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                           static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, att));
+                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
     if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_fc1, L.b_fc1, nullptr, ff, B, 4 * d, ACT_GELU, 0, st, light))) return rc;

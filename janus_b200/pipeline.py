@@ -82,7 +82,7 @@ class _Lane:
         self.stream = torch.cuda.Stream(dev)
         with torch.cuda.stream(self.stream):
             self.session = DecodeSession(enc.whisper, enc.lane_batch, enc.max_new_tokens, light=enc.light,
-                                         steps_per_graph=enc.steps_per_graph)
+                                         steps_per_graph=enc.steps_per_graph, fused=enc.fused)
             self.session._ensure_graph()
         self.stream.synchronize()
         self.ready = torch.cuda.Event()    # encoder stream -> lane: cross-KV of this lane is written
@@ -109,7 +109,8 @@ class SemanticEncoder:
     def __init__(self, model: str | WhisperDims = "small", batch: int = 64, max_new_tokens: int = 128,
                  device=None, seed: int = 0, weights: dict | None = None, weight_profile: str = "confident",
                  prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, lane_batch: int = 64,
-                 n_lanes: int | None = None, steps_per_graph: int = 10, light: bool | None = None) -> None:
+                 n_lanes: int | None = None, steps_per_graph: int = 10, light: bool | None = None,
+                 fused: bool = False, enc_chunk: int = 64) -> None:
         self.dims = PRESETS[model] if isinstance(model, str) else model
         self.spec = tokenizer_spec(self.dims)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -123,7 +124,8 @@ class SemanticEncoder:
         self.n_lanes = n_lanes if n_lanes is not None else 2 * self.lanes_per_call
         if self.n_lanes < self.lanes_per_call:
             raise ValueError("n_lanes must be >= batch / lane_batch")
-        self.light = (self.lane_batch <= 64) if light is None else light
+        self.fused = fused
+        self.light = (self.lane_batch <= 64 and not fused) if light is None else light
         self.max_new_tokens, self.steps_per_graph = max_new_tokens, steps_per_graph
         self.decim = input_sample_rate // 16000
         assert input_sample_rate in (16000, 48000)
@@ -136,10 +138,13 @@ class SemanticEncoder:
             self.enc_stream = torch.cuda.Stream(self.device, priority=-1)
             self.lanes = [_Lane(self, i) for i in range(self.n_lanes)]
             self._next_lane = 0
+            self._last_decode = None
             lb = self.lane_batch
-            # encoder-stream buffers, shared by all lanes (the encoder stream is in-order)
-            self.mel_pad = torch.empty((lb, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16, device=self.device)
-            self.mel_scratch = torch.empty((lb, self.whisper.frontend.frames_alloc, d.n_mels), dtype=torch.float32,
+            # the encoder is tensor-bound and runs in micro-batches of `enc_chunk` windows (bounded workspace);
+            # encoder-stream buffers are shared by all lanes (the encoder stream is in-order)
+            self.enc_chunk = ec = min(enc_chunk, lb)
+            self.mel_pad = torch.empty((ec, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16, device=self.device)
+            self.mel_scratch = torch.empty((ec, self.whisper.frontend.frames_alloc, d.n_mels), dtype=torch.float32,
                                            device=self.device)
             self.enc_out = torch.empty((lb, d.n_audio_ctx, d.n_audio_state), dtype=torch.bfloat16, device=self.device)
             self.max_new = self.lanes[0].session.max_new
@@ -165,7 +170,9 @@ class SemanticEncoder:
         return p
 
     def kernels_per_step(self) -> int:
-        enc = self.lanes_per_call * (2 + 2 + 2 + 7 * self.dims.n_audio_layer + 1 + 1)  # prosody, log-mel, stem, layers, ln_post, cross-KV
+        chunks = -(-self.lane_batch // self.enc_chunk)
+        # prosody (2), cross-KV (1) per lane; log-mel (2), stem (2), layers, ln_post per encoder micro-batch
+        enc = self.lanes_per_call * (3 + chunks * (2 + 2 + 7 * self.dims.n_audio_layer + 1))
         ses = self.lanes[0].session
         return enc + self.lanes_per_call * ses.n_steps * ses.kernels_per_step
 
@@ -178,9 +185,17 @@ class SemanticEncoder:
             out = lane.pros_out[lengths] = self.prosody.alloc_outputs(plan)
         lane.cur_pros = out
         self.prosody.run(pcm, plan, out=out)
-        self.whisper.frontend(pcm, offs, lens, decim=self.decim, scratch=self.mel_scratch, out_bf16=self.mel_pad)
-        self.whisper.encode(self.mel_pad, out=self.enc_out)
+        self.encode_lane_windows(pcm, offs, lens)
         lane.session.cross_kv(self.enc_out)
+
+    def encode_lane_windows(self, pcm: torch.Tensor, offs: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
+        """K1 + K2 over one lane's windows in encoder micro-batches; fills self.enc_out [lane_batch, n_ctx, d]."""
+        for c0 in range(0, self.lane_batch, self.enc_chunk):
+            n = min(self.enc_chunk, self.lane_batch - c0)
+            self.whisper.frontend(pcm, offs[c0:c0 + n], lens[c0:c0 + n], decim=self.decim, scratch=self.mel_scratch[:n],
+                                  out_bf16=self.mel_pad[:n])
+            self.whisper.encode(self.mel_pad[:n], out=self.enc_out[c0:c0 + n])
+        return self.enc_out
 
     def encode_device(self, pcm: torch.Tensor, lengths, host_pcm: torch.Tensor | None = None) -> EncodeResult:
         """pcm: float32 device tensor holding the `batch` windows concatenated (source-rate samples);
@@ -212,6 +227,10 @@ class SemanticEncoder:
                 lane.ready.record(self.enc_stream)
             with torch.cuda.stream(lane.stream):
                 lane.stream.wait_event(lane.ready)
+                if self.fused and self._last_decode is not None:
+                    # the fused segment kernels wait on each other across CTAs (grid barrier): keep at most one
+                    # decode chain in flight so that two chains can never hold partial sets of SMs
+                    lane.stream.wait_event(self._last_decode)
                 ses = lane.session
                 ses.reset()
                 ses.run_steps()
@@ -221,6 +240,7 @@ class SemanticEncoder:
                 tags[r].copy_(lane.cur_pros["tags"], non_blocking=True)
                 lane.free = torch.cuda.Event()
                 lane.free.record(lane.stream)
+                self._last_decode = lane.free
                 events.append(lane.free)
             start += n
         return EncodeResult(tokens, sum_lp, tags, events)

@@ -123,7 +123,8 @@ class DecWeightsStruct(C.Structure):
 
 
 class DecodeStateStruct(C.Structure):
-    _fields_ = [("batch", C.c_int32), ("max_len", C.c_int32), ("n_prompt", C.c_int32), ("flags", C.c_int32)] + \
+    _fields_ = [("batch", C.c_int32), ("max_len", C.c_int32), ("n_prompt", C.c_int32), ("flags", C.c_int32),
+                ("self_ld", C.c_int32), ("reserved0", C.c_int32)] + \
                [(n, C.c_void_p) for n in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done",
                                           "n_done", "self_k", "self_v", "cross_k", "cross_v", "x", "xn", "qkv",
                                           "att", "q", "ff", "logits", "barrier")]
@@ -202,8 +203,9 @@ class DecodeSession:
         self.pos = torch.zeros(1, **i32)
         self.done = torch.zeros(B, dtype=torch.uint8, device=dev)
         self.n_done = torch.zeros(1, **i32)
-        self.self_k = torch.zeros((L, B, H, d.n_text_ctx, 64), **bf)
-        self.self_v = torch.zeros((L, B, H, d.n_text_ctx, 64), **bf)
+        self.self_ld = min(d.n_text_ctx, -(-self.max_len // 8) * 8)   # cache only the positions this session can reach
+        self.self_k = torch.zeros((L, B, H, self.self_ld, 64), **bf)
+        self.self_v = torch.zeros((L, B, H, self.self_ld, 64), **bf)
         self.cross_k = torch.zeros((L, B, H, 64, engine.kv_ld), **bf)
         self.cross_v = torch.zeros((L, B, H, d.n_audio_ctx, 64), **bf)
         self.x, self.xn = torch.zeros((B, n), **bf), torch.zeros((B, n), **bf)
@@ -213,6 +215,7 @@ class DecodeSession:
         self.prompt = torch.tensor(list(spec.sot_sequence), **i32)
         s = DecodeStateStruct()
         s.batch, s.max_len, s.n_prompt = B, self.max_len, self.n_prompt
+        s.self_ld = self.self_ld
         if light and B > 64:
             raise ValueError("light decode sessions hold at most 64 streams")
         s.flags = (self.DECODE_LIGHT if light else 0) | (self.DECODE_FUSED if fused else 0)
