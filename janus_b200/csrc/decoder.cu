@@ -134,7 +134,7 @@ dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ 
   float acc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  if (key0 < kv_ld) {
+  if (key0 < T) {   // (threads whose 8 keys are all padding load nothing)
     const uint4* kp = reinterpret_cast<const uint4*>(kT + bh * DH * kv_ld + key0);
     const int stride = kv_ld >> 3;  // uint4 per dim row
 #pragma unroll 16
