@@ -45,16 +45,27 @@ __global__ void dec_embed_kernel(const int32_t* tokens, int max_len, const int32
 }
 
 // ------------------------------------------------------------------------------------------
-// causal self-attention over the KV cache: one warp per (head, stream)
+// causal self-attention over the KV cache: one warp per (stream, head), 4 per CTA
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(32)
+// At 1024 streams this is 12288 independent (stream, head) problems of <= 131 keys each per layer: a
+// streaming kernel (~200 MB of cache per launch), so what matters is resident warps and loads in flight:
+// scores with one key row (128 B) per lane, PV with 4 rows x 16 B per lane-group and 4-way unrolling.
+constexpr int SA_WARPS = 4;
+constexpr int SA_MAXCTX = 512;
+
+__global__ void __launch_bounds__(SA_WARPS * 32)
 dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos_p, int d,
-                     int n_ctx, __nv_bfloat16* out) {
-  __shared__ float ps[512];
-  __shared__ float qs[DH];
-  const int h = blockIdx.x, b = blockIdx.y, H = gridDim.x, lane = threadIdx.x;
+                     int n_ctx, int H, int n_items, __nv_bfloat16* out) {
+  __shared__ float ps_all[SA_WARPS][SA_MAXCTX];
+  __shared__ float qs_all[SA_WARPS][DH];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   pdl_launch_dependents();
   pdl_wait();
+  const int item = blockIdx.x * SA_WARPS + warp;
+  if (item >= n_items) return;
+  float* ps = ps_all[warp];
+  float* qs = qs_all[warp];
+  const int b = item / H, h = item - b * H;
   const int pos = *pos_p;
   const __nv_bfloat16* row = qkv + (long long)b * 3 * d + h * DH;
   __nv_bfloat16* K = kc + ((long long)b * H + h) * n_ctx * DH;
@@ -71,11 +82,13 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
   float mx = -INFINITY;
   for (int j = lane; j <= pos; j += 32) {
     const uint4* kr = reinterpret_cast<const uint4*>(K + (long long)j * DH);
+    uint4 u[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) u[c] = kr[c];
     float s = 0.f;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-      const uint4 u = kr[c];
-      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u[c]);
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const float2 f = __bfloat1622float2(hh[e]);
@@ -95,15 +108,37 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
   }
   sum = warp_sum(sum);
   __syncwarp();
-  float o0 = 0.f, o1 = 0.f;
-  for (int j = 0; j <= pos; ++j) {
-    const float2 f = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(V + (long long)j * DH)[lane]);
+  // PV: lane group jg = lane / 8 takes rows jg, jg + 4, ...; lane c = lane % 8 owns dims 8c .. 8c+7
+  const int jg = lane >> 3, c8 = lane & 7;
+  float o[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] = 0.f;
+  const uint4* vp = reinterpret_cast<const uint4*>(V) + c8;
+#pragma unroll 4
+  for (int j = jg; j <= pos; j += 4) {
+    const uint4 u = vp[(long long)j * 8];
     const float p = ps[j];
-    o0 = fmaf(p, f.x, o0);
-    o1 = fmaf(p, f.y, o1);
+    const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(hh[e]);
+      o[2 * e] = fmaf(p, f.x, o[2 * e]);
+      o[2 * e + 1] = fmaf(p, f.y, o[2 * e + 1]);
+    }
   }
-  const float inv = 1.f / sum;
-  reinterpret_cast<__nv_bfloat162*>(out + (long long)b * d + h * DH)[lane] = __floats2bfloat162_rn(o0 * inv, o1 * inv);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    o[i] += __shfl_xor_sync(FULL_MASK, o[i], 8);
+    o[i] += __shfl_xor_sync(FULL_MASK, o[i], 16);
+  }
+  if (jg == 0) {
+    const float inv = 1.f / sum;
+    uint4 w;
+    __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&w);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) hh[e] = __floats2bfloat162_rn(o[2 * e] * inv, o[2 * e + 1] * inv);
+    reinterpret_cast<uint4*>(out + (long long)b * d + h * DH)[c8] = w;
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -385,7 +420,12 @@ static int linear(const __nv_bfloat16* A, int K, const void* W, const float* bia
   q.M_per_batch = rows; q.n_batch = 1; q.N = N; q.K = K;
   q.out = static_cast<__nv_bfloat16*>(out); q.ldc = N; q.out_batch_stride = (long long)rows * N;
   q.bias = bias; q.residual = residual; q.act = act; q.store_mode = out_f32 ? STORE_F32 : STORE_ROWMAJOR;
+  // N tile: the widest of 256 / 128 / 64 that still yields about one CTA per SM (skinny M: many small tiles
+  // beat few wide ones); at >= 512 rows the wide vocabulary / QKV / MLP projections fill the machine with 128-256
+  const int m_tiles = (rows + 127) / 128;
   q.bn_max = 64;
+  for (int bn = 256; bn > 64; bn >>= 1)
+    if (N % bn == 0 && (long long)m_tiles * (N / bn) >= (num_sms() * 9) / 10) { q.bn_max = bn; break; }
   return gemm_bf16(A, K, (long long)rows * K, static_cast<const __nv_bfloat16*>(W), K, q, st);
 }
 
@@ -499,9 +539,9 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
     const janus_dec_layer_t& L = w->layers[l];
     if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st, light))) return rc;
-    JANUS_CUDA(launch_pdl(dec_self_attn_kernel, dim3(H, B), dim3(32), 0, st, qkv,
+    JANUS_CUDA(launch_pdl(dec_self_attn_kernel, dim3((H * B + SA_WARPS - 1) / SA_WARPS), dim3(SA_WARPS * 32), 0, st, qkv,
                           static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
-                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, att));
+                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, H, H * B, att));
     if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st, light))) return rc;

@@ -153,7 +153,7 @@ def _pack_decoder(self, W) -> None:
         ckv_w += [W[p + ".cross.k.w"], W[p + ".cross.v.w"]]
         ckv_b += [torch.zeros(n), W[p + ".cross.v.b"]]
     dw = DecWeightsStruct()
-    vpad = -(-d.n_vocab // 64) * 64
+    vpad = -(-d.n_vocab // 256) * 256   # multiple of the widest GEMM N tile (zero rows: logits 0, never picked)
     emb = torch.zeros(vpad, n)
     emb[:d.n_vocab] = W["dec.tok_emb"]
     dw.tok_emb = self._bf16(emb).data_ptr()
