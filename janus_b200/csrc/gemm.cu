@@ -31,7 +31,10 @@ struct GemmSmem {
   static constexpr int B_BYTES = BN * GEMM_BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
-  static constexpr int BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  // BN >= 128: each epilogue warp owns a 32-row x 128-byte staging slab (128B-swizzled) so that row-major
+  // bf16 results / residuals move to and from global memory as full 128-byte lines
+  static constexpr int EPI_BYTES = BN >= 128 ? GEMM_EPI_WARPS * 4096 : 0;
+  static constexpr int BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
 template <int BN>
@@ -41,7 +44,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   using S = GemmSmem<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + S::STAGES * S::STAGE_BYTES);
+  uint8_t* epi_stage = smem + S::STAGES * S::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_stage + S::EPI_BYTES);
   uint64_t* full = bars;                       // [STAGES]
   uint64_t* empty = bars + S::STAGES;          // [STAGES]
   uint64_t* tmem_full = bars + 2 * S::STAGES;  // [2]
@@ -139,6 +143,97 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       tc_fence_after();
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
       const long long row_off = (long long)b * p.out_batch_stride + (long long)(t + p.out_row_offset) * p.ldc;
+      if (BN >= 128 && p.store_mode == STORE_ROWMAJOR) {
+        // ---- coalesced path: 64 output columns (one 128-byte line per row) at a time through the warp's
+        // swizzled staging slab. A thread owns row `lane` while computing (TMEM lane = row) and the
+        // 16-byte chunk (lane & 7) of rows 4*it + (lane >> 3) while talking to global memory.
+        uint8_t* slab = epi_stage + (warp - 2) * 4096;
+        const uint32_t slab_u = smem_u32(slab);
+        const int grow0 = m_tile * GEMM_BM + q * 32;                   // first row of this warp within the batch
+        const long long base_off = (long long)b * p.out_batch_stride + (long long)(grow0 + p.out_row_offset) * p.ldc;
+        const int cr = lane >> 3, cc = lane & 7;
+#pragma unroll 1
+        for (int g0 = chalf * (BN / 2); g0 < (chalf + 1) * (BN / 2); g0 += 64) {
+          const int n0 = n_tile * BN + g0;
+          if (p.residual) {   // global (full lines) -> slab
+            uint4 ru[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int rr = 4 * it + cr;
+              ru[it] = make_uint4(0, 0, 0, 0);
+              if (grow0 + rr < p.M_per_batch)
+                ru[it] = __ldg(reinterpret_cast<const uint4*>(p.residual + base_off + (long long)rr * p.ldc + n0) + cc);
+            }
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int rr = 4 * it + cr;
+              *reinterpret_cast<uint4*>(slab + rr * 128 + ((cc ^ (rr & 7)) << 4)) = ru[it];
+            }
+            __syncwarp();
+          }
+#pragma unroll
+          for (int hc = 0; hc < 2; ++hc) {   // two 32-column halves of the 64-column group
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + g0 + 32 * hc, r);
+            float4 bb[8];
+            if (p.bias) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) bb[i] = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 32 * hc) + i);
+            }
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+            if (p.bias) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                v[4 * i] += bb[i].x; v[4 * i + 1] += bb[i].y; v[4 * i + 2] += bb[i].z; v[4 * i + 3] += bb[i].w;
+              }
+            }
+            if (p.act == ACT_GELU) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = gelu_erf_fast(v[i]);
+            }
+            if (p.pos && row_ok) {
+              const float* pp = p.pos + (long long)t * p.N + n0 + 32 * hc;
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(pp + i));
+                v[i] += b4.x; v[i + 1] += b4.y; v[i + 2] += b4.z; v[i + 3] += b4.w;
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {   // this row's chunks 4*hc + i
+              const uint32_t addr = slab_u + lane * 128 + (((4 * hc + i) ^ (lane & 7)) << 4);
+              if (p.residual) {
+                uint4 u;
+                asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "r"(addr) : "memory");
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 f = __bfloat1622float2(h[j]);
+                  v[i * 8 + 2 * j] += f.x;
+                  v[i * 8 + 2 * j + 1] += f.y;
+                }
+              }
+              uint4 o;
+              __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) ho[j] = __floats2bfloat162_rn(v[i * 8 + 2 * j], v[i * 8 + 2 * j + 1]);
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+            }
+          }
+          __syncwarp();
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {   // slab -> global, 4 full 128-byte lines per instruction
+            const int rr = 4 * it + cr;
+            const uint4 u = *reinterpret_cast<const uint4*>(slab + rr * 128 + ((cc ^ (rr & 7)) << 4));
+            if (grow0 + rr < p.M_per_batch)
+              *(reinterpret_cast<uint4*>(p.out + base_off + (long long)rr * p.ldc + n0) + cc) = u;
+          }
+          __syncwarp();
+        }
+      } else
 #pragma unroll 1
       for (int c0 = chalf * (BN / 2); c0 < (chalf + 1) * (BN / 2); c0 += 32) {
         uint32_t r[32];
@@ -157,7 +252,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         if (p.act == ACT_GELU) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = gelu_erf(v[i]);
+          for (int i = 0; i < 32; ++i) v[i] = gelu_erf_fast(v[i]);
         }
         if (row_ok) {
           if (p.pos) {

@@ -36,3 +36,17 @@ if __name__ == "__main__":
     run(M, 768, 3072, res=True)
     run(M, 18432, 768, bias=False, iters=5)
     run(8192, 8192, 8192, bias=False, iters=5)
+    # encoder attention at the micro-batch shape (64 windows x 1500 x 12 heads)
+    B, T, H = 64, 1500, 12
+    qkv = torch.randn(B, T, 3 * H * 64, device="cuda").bfloat16()
+    o = torch.empty(B, T, H * 64, device="cuda", dtype=torch.bfloat16)
+    st = torch.cuda.current_stream().cuda_stream
+    fa = lambda: _abi.call("janus_attention_enc_bf16", qkv.data_ptr(), o.data_ptr(), B, T, H, st)
+    for _ in range(3): fa()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20): fa()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 20
+    print(f"attention_enc B={B}: {ms:.3f} ms  {4.0 * T * T * 64 * H * B / ms / 1e9:.0f} TFLOP/s")
