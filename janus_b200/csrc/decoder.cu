@@ -79,26 +79,34 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
     qs[2 * lane + 1] = qq.y * 0.125f;
   }
   __syncwarp();
-  float mx = -INFINITY;
-  for (int j = lane; j <= pos; j += 32) {
-    const uint4* kr = reinterpret_cast<const uint4*>(K + (long long)j * DH);
-    uint4 u[8];
+  // scores: 8 lanes share one 128-byte key row (fully coalesced: 4 rows per load instruction), partial dot
+  // products over 8 dims each, 3 shuffles per row. (One row per lane costs 32 L1 wavefronts per 16-byte
+  // load and capped the kernel at half the HBM rate.)
+  const int jg = lane >> 3, c8 = lane & 7;
+  float qf[8];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) u[c] = kr[c];
+  for (int i = 0; i < 8; ++i) qf[i] = qs[c8 * 8 + i];
+  const uint4* kp = reinterpret_cast<const uint4*>(K) + c8;
+#pragma unroll 4
+  for (int j0 = 0; j0 <= pos; j0 += 4) {   // warp-uniform trip count (the shuffles below need every lane)
+    const int j = j0 + jg;
+    const uint4 u = j <= pos ? kp[(long long)j * 8] : make_uint4(0, 0, 0, 0);
+    const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
     float s = 0.f;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u[c]);
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 f = __bfloat1622float2(hh[e]);
-        s = fmaf(f.x, qs[c * 8 + 2 * e], s);
-        s = fmaf(f.y, qs[c * 8 + 2 * e + 1], s);
-      }
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(hh[e]);
+      s = fmaf(f.x, qf[2 * e], s);
+      s = fmaf(f.y, qf[2 * e + 1], s);
     }
-    ps[j] = s;
-    mx = fmaxf(mx, s);
+    s += __shfl_xor_sync(FULL_MASK, s, 1);
+    s += __shfl_xor_sync(FULL_MASK, s, 2);
+    s += __shfl_xor_sync(FULL_MASK, s, 4);
+    if (c8 == 0 && j <= pos) ps[j] = s;
   }
+  __syncwarp();
+  float mx = -INFINITY;
+  for (int j = lane; j <= pos; j += 32) mx = fmaxf(mx, ps[j]);
   mx = warp_max(mx);
   float sum = 0.f;
   for (int j = lane; j <= pos; j += 32) {
@@ -109,7 +117,6 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
   sum = warp_sum(sum);
   __syncwarp();
   // PV: lane group jg = lane / 8 takes rows jg, jg + 4, ...; lane c = lane % 8 owns dims 8c .. 8c+7
-  const int jg = lane >> 3, c8 = lane & 7;
   float o[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) o[i] = 0.f;
