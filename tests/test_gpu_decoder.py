@@ -201,3 +201,19 @@ def test_fused_segment_matches_per_op_path_many_rows(batch):
     choice = b.choice[:, b.n_prompt:]
     agree = float((choice == ta).float().mean())
     assert agree > 0.98, agree
+
+
+def test_long_decode_positions_past_128():
+    """140 generated tokens: self-attention positions cross 128 (several 32-key score passes, 4-row PV groups
+    with ragged tails); greedy tokens still equal the fp32 oracle's under confident weights."""
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, clips, mel, enc_ref, eng, R = _setup("confident", 3, n_clips=2)
+    n_new = 140
+    ref_tok, ref_lp, _ = R.greedy_decode(W, dims, spec, enc_ref, n_new, stop_at_eot=False, return_margins=True)
+    enc_bf16 = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    ses = DecodeSession(eng, batch=2, max_new_tokens=n_new, steps_per_graph=16)
+    toks, _ = ses.decode(enc_bf16, forced=ref_tok.cuda())
+    torch.cuda.synchronize()
+    choice = ses.choice[:, ses.n_prompt:].cpu().long()
+    agree = float((choice == ref_tok).float().mean())
+    assert agree > 0.97, agree
