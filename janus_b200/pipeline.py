@@ -251,9 +251,20 @@ class SemanticEncoder:
             lane.stream.synchronize()
 
     def to_packets(self, tokens_host: np.ndarray, tags_host: np.ndarray, timestamps=None,
-                   mode: JanusMode = JanusMode.SEMANTIC_VOICE, override_emotion=None):
+                   mode: JanusMode = JanusMode.SEMANTIC_VOICE, override_emotion=None,
+                   avg_pitch_hz: np.ndarray | None = None, avg_energy: np.ndarray | None = None):
+        """Token ids + tag ids -> texts and MessagePack packets. `avg_pitch_hz` / `avg_energy` (per stream)
+        opt in to the richer prosody the reference's receiver already reads but its sender never fills
+        (/root/reference/backend/services/engine.py:231-233,554-560): off by default, because
+        the extra keys change the packet bytes."""
         texts = [join_segments(split_text_segments(row, self.spec)) for row in tokens_host]
         pros = [{'energy': ENERGY_TAGS[e], 'pitch': PITCH_TAGS[p]} for e, p in tags_host]
+        if avg_pitch_hz is not None or avg_energy is not None:
+            for i, d_ in enumerate(pros):
+                if avg_pitch_hz is not None:
+                    d_['avg_pitch_hz'] = float(avg_pitch_hz[i])
+                if avg_energy is not None:
+                    d_['avg_energy'] = float(avg_energy[i])
         return texts, pack_packets(texts, pros, mode, override_emotion, timestamps)
 
     def encode_host(self, buffers: list[np.ndarray], timestamps=None):

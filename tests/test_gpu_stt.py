@@ -107,3 +107,36 @@ def test_encoder_vs_fp32_oracle(name):
     err = (out - ref).abs()
     print(f"encoder {dims.name}: mean err {err.mean():.4g} max err {err.max():.4g} ref std {ref.std():.3f}")
     assert err.mean() <= 1.5e-2 and err.max() <= 0.25
+
+
+def test_large_v3_shape_end_to_end():
+    """BASELINE configs[3] architecture family (d = 1280, 20 heads, 128 mel bins, 51866 tokens) at 1 layer:
+    K1 log-mel with 128 filters, encoder vs the fp32 oracle, and greedy tokens from audio under confident
+    weights. (The 32-layer model only repeats these blocks.)"""
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.engine import DecodeSession, WhisperEngine
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = test_dims(d=1280, heads=20, layers=1, n_mels=128, vocab=51866)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=4, profile="confident")
+    clips = _clips()[:2]
+    mel = torch.stack([torch.from_numpy(log_mel_window(c, dims.n_mels)) for c in clips])
+    ref = R.encode(W, dims, mel)
+    eng = WhisperEngine(dims, W, torch.device("cuda", 0))
+    dev = eng.device
+    lens = torch.tensor([len(c) for c in clips], dtype=torch.int64)
+    offs = torch.cumsum(lens, 0) - lens
+    pcm = torch.from_numpy(np.concatenate(clips)).to(dev)
+    mel_pad, _ = eng.frontend(pcm, offs.to(dev), lens.to(dev))
+    enc = eng.encode(mel_pad)
+    err = (enc.float().cpu() - ref).abs()
+    print(f"large-v3-shaped encoder: mean err {err.mean():.4g} max err {err.max():.4g}")
+    assert err.mean() <= 1.5e-2 and err.max() <= 0.3
+    n_new = 12
+    ref_tok, _ = R.greedy_decode(W, dims, spec, ref, n_new)
+    ses = DecodeSession(eng, batch=2, max_new_tokens=n_new)
+    toks, _ = ses.decode(enc)
+    torch.cuda.synchronize()
+    assert torch.equal(toks.cpu().long(), ref_tok)
