@@ -47,7 +47,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for src in sources():
         obj = os.path.join(OUT_DIR, os.path.basename(src)[:-3] + ".o")
-        cmd = [NVCC, *NVCC_FLAGS, "-c", src, "-o", obj]
+        cmd = [NVCC, *NVCC_FLAGS, *os.environ.get("JANUS_NVCC_EXTRA", "").split(), "-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd))

@@ -26,11 +26,18 @@ namespace janus {
 constexpr int ATT_BQ = 256;   // queries per CTA: two 128-row tiles, one per softmax warpgroup
 constexpr int ATT_BK = 128;
 constexpr int ATT_DH = 64;
-constexpr int ATT_KV_STAGES = 3;
-constexpr int ATT_THREADS = 256;  // two softmax warpgroups; thread 0 of each also issues its TMA / tcgen05.mma
+constexpr int ATT_KV_STAGES = 4;
+constexpr int ATT_SOFTMAX_THREADS = 256;  // two softmax warpgroups (one thread per query row)
+// + warpgroup 2: one thread of warp 8 issues every TMA load and tcgen05.mma. Registers are allocated per
+// warpgroup, so a 9th warp costs a whole warpgroup's worth: the kernel launches at 168 registers x 384 threads
+// and setmaxnreg moves the issuer warpgroup's share (it needs < 40) to the softmax warpgroups (128 fp32 scores
+// per thread live in registers).
+constexpr int ATT_THREADS = ATT_SOFTMAX_THREADS + 128;
+constexpr int ATT_REGS_ISSUER = 40;
+constexpr int ATT_REGS_SOFTMAX = 232;   // 128*40 + 256*232 == 384*168
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: a Q, K or V tile
 // Q0 Q1 | (K V) x stages | P0 P1 (32 KB each) | barriers
-constexpr int ATT_SMEM = ATT_TILE_BYTES * (2 + 2 * ATT_KV_STAGES + 4) + 256;
+constexpr int ATT_SMEM = ATT_TILE_BYTES * (2 + 2 * ATT_KV_STAGES) + 256;
 constexpr float ATT_RESCALE_LOG2 = 8.0f;  // lazy rescale threshold: p = exp2(.) stays below 2^8
 
 __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
@@ -76,22 +83,63 @@ __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory");
 }
 
+// ---- exp2 on the FMA pipe. x <= ~8 (lazy rescale bound); clamped at -126 so that the exponent arithmetic
+// cannot wrap (a masked key's -inf becomes 2^-126, which vanishes against the row sum and multiplies a
+// zero-filled V row). Round to nearest integer with the 1.5*2^23 trick, degree-3 minimax polynomial for
+// 2^f on [-0.5, 0.5] (max rel. error 7.5e-5 = 2^-13.7, far inside bf16's 2^-9), exponent added to the bits.
+#ifndef ATT_POLY_MODE
+#define ATT_POLY_MODE 2
+#endif
+__device__ __forceinline__ constexpr bool att_poly_pair(int i) {   // i = pair index 0..63 within the key tile
+  return ATT_POLY_MODE == 0 ? false
+       : ATT_POLY_MODE == 1 ? (i & 3) == 0                       // 25 %
+       : ATT_POLY_MODE == 2 ? ((i & 3) == 0 || (i & 7) == 5)     // 37.5 %
+                            : (i & 1) == 0;                       // 50 %
+}
+__device__ __forceinline__ void att_exp2_poly(uint64_t x2, float& p0, float& p1) {
+  float x0, x1;
+  unpack_f32x2(x2, x0, x1);
+  x0 = fmaxf(x0, -126.f);
+  x1 = fmaxf(x1, -126.f);
+  const uint64_t xc = pack_f32x2(x0, x1);
+  const uint64_t r2 = add_f32x2(xc, pack_f32x2(12582912.f, 12582912.f));            // low mantissa bits = round(x)
+  const uint64_t fl = add_f32x2(r2, pack_f32x2(-12582912.f, -12582912.f));
+  const uint64_t f2 = fma_f32x2(fl, pack_f32x2(-1.f, -1.f), xc);                    // f in [-0.5, 0.5]
+  uint64_t q = fma_f32x2(pack_f32x2(0.0551716685295105f, 0.0551716685295105f), f2,
+                         pack_f32x2(0.2426111251115799f, 0.2426111251115799f));
+  q = fma_f32x2(q, f2, pack_f32x2(0.6932609677314758f, 0.6932609677314758f));
+  q = fma_f32x2(q, f2, pack_f32x2(0.9999280571937561f, 0.9999280571937561f));
+  float r0, r1, q0, q1;
+  unpack_f32x2(r2, r0, r1);
+  unpack_f32x2(q, q0, q1);
+  p0 = __uint_as_float(__float_as_uint(q0) + (__float_as_uint(r0) << 23));
+  p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(r1) << 23));
+}
+
+#ifdef ATT_PROFILE
+__device__ long long att_dbg[8 * 8];
+__device__ long long att_dbg2[8];
+#endif
+
 __global__ void __launch_bounds__(ATT_THREADS, 1)
 attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out, int T, int d,
                      float scale_log2) {
+#ifdef ATT_PROFILE
+  const long long t_entry = clock64();
+#endif
   extern __shared__ __align__(1024) uint8_t smem[];  // 128B-swizzled tiles need 1024 B alignment
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* sQ[2] = {smem, smem + ATT_TILE_BYTES};
   uint8_t* sKV = smem + 2 * ATT_TILE_BYTES;                       // stage s: K at +2s, V at +2s+1 tiles
-  uint8_t* sP[2] = {sKV + 2 * ATT_KV_STAGES * ATT_TILE_BYTES, sKV + (2 * ATT_KV_STAGES + 2) * ATT_TILE_BYTES};
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + (2 * ATT_KV_STAGES + 4) * ATT_TILE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKV + 2 * ATT_KV_STAGES * ATT_TILE_BYTES);
   uint64_t* q_full = bars;                    // [1]
   uint64_t* kv_full = bars + 1;               // [stages]
   uint64_t* kv_empty = kv_full + ATT_KV_STAGES;
   uint64_t* s_full = kv_empty + ATT_KV_STAGES;  // [2]
   uint64_t* p_full = s_full + 2;                // [2]
   uint64_t* o_ready = p_full + 2;               // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_ready + 2);
+  uint64_t* s_free = o_ready + 2;               // [2]  all 4 warps of the warpgroup hold S(j) in registers
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_free + 2);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -111,6 +159,7 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
       mbar_init(&o_ready[i], 1);
+      mbar_init(&s_free[i], 4);
     }
     fence_mbar_init();
   }
@@ -119,14 +168,17 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  // TMEM columns: S0 [0,128)  S1 [128,256)  O0 [256,320)  O1 [320,384)
+  // TMEM columns: S0 [0,128)  S1 [128,256)  O0 [256,320)  O1 [320,384)  P0 [384,448)  P1 [448,512)
+  // P (bf16 probabilities, two keys per 32-bit column) is the A operand of the PV MMA straight from tensor
+  // memory: with P in shared memory the kernel moved 256 KB per key tile through the 128 B/clk smem port
+  // (Q, K, V and P operand reads, the P stores and the TMA fills) -- as long as the MUFU floor.
 
-  const int w = warp >> 2;                 // warpgroup 0 / 1 == query tile
-  const bool issuer = (warp & 3) == 0 && lane == 0;   // one thread per warpgroup drives its MMAs
+  const int w = (warp >> 2) & 1;           // warpgroup 0 / 1 == query tile (softmax warps 0..7)
   const int r = threadIdx.x & 127;         // row within the 128-query tile == TMEM lane
   const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
   const uint32_t tmem_s = tmem_base + w * 128 + lane_off;
   const uint32_t tmem_o = tmem_base + 256 + w * 64 + lane_off;
+  const uint32_t tmem_p = tmem_base + 384 + w * 64 + lane_off;
   constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
   constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
 
@@ -137,63 +189,105 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
     tma_load_3d(k, &tmap_qkv, &kv_full[s], d + h * ATT_DH, j * ATT_BK, b);
     tma_load_3d(k + ATT_TILE_BYTES, &tmap_qkv, &kv_full[s], 2 * d + h * ATT_DH, j * ATT_BK, b);
   };
-  auto issue_s = [&](int j) {   // S_w = Q_w K_j^T
+  auto issue_s = [&](int w, int j) {   // S_w = Q_w K_j^T
     const uint64_t dq = umma_smem_desc_sw128(smem_u32(sQ[w]));
     const uint64_t dk = umma_smem_desc_sw128(smem_u32(sKV + 2 * (j % ATT_KV_STAGES) * ATT_TILE_BYTES));
 #pragma unroll
     for (int k = 0; k < 4; ++k) umma_f16(tmem_base + w * 128, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
     umma_commit(&s_full[w]);
   };
-  auto issue_pv = [&](int j) {  // O_w (+)= P_w V_j
+  auto issue_pv = [&](int w, int j) {  // O_w (+)= P_w V_j
     const uint32_t v_addr = smem_u32(sKV + (2 * (j % ATT_KV_STAGES) + 1) * ATT_TILE_BYTES);
-    const uint32_t p_addr = smem_u32(sP[w]);
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
-      const uint64_t dp = umma_smem_desc_sw128(p_addr + (ks >> 2) * ATT_TILE_BYTES) + 2 * (ks & 3);
-      const uint64_t dv = umma_smem_desc_sw128(v_addr + ks * 2048);
-      umma_f16(tmem_base + 256 + w * 64, dp, dv, idesc_pv, (j | ks) != 0);
-    }
+    for (int ks = 0; ks < 8; ++ks)   // 16 keys = 8 TMEM columns of P, 2048 B of the MN-major V tile
+      umma_f16_ts(tmem_base + 256 + w * 64, tmem_base + 384 + w * 64 + ks * 8, umma_smem_desc_sw128(v_addr + ks * 2048),
+                  idesc_pv, (j | ks) != 0);
     umma_commit(&o_ready[w]);
     umma_commit(&kv_empty[j % ATT_KV_STAGES]);
   };
 
-  // ---- prologue: Q tiles, the first K/V stages, and each warpgroup's first S
-  if (issuer) {
-    if (w == 0) {
-      mbar_arrive_expect_tx(q_full, 2 * ATT_TILE_BYTES);
-      tma_load_3d(sQ[0], &tmap_qkv, q_full, h * ATT_DH, q0, b);
-      tma_load_3d(sQ[1], &tmap_qkv, q_full, h * ATT_DH, q0 + 128, b);
-      for (int j = 0; j < ATT_KV_STAGES && j < n_tiles; ++j) load_kv(j);
+  // ---- warp 8: the only thread that talks to the TMA unit and the tensor core. tcgen05.mma issue
+  // back-pressures the issuing thread while the tensor core is busy (measured: ~1800 cycles per tile
+  // when a softmax thread did the issuing), so it must not sit on the softmax critical path.
+  if (warp >= 8) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(ATT_REGS_ISSUER));
+    // Warps 8 / 9 issue the MMAs of query tile 0 / 1, warp 10 runs the K/V ring. Each is a straight sequence of
+    // blocking mbarrier waits (a suspended wait costs no issue slots, a polling loop over several barriers
+    // measured ~1700 cycles per round because it competes with the softmax warps of its scheduler), run by
+    // the whole warp so that descriptors and TMEM addresses stay in uniform registers (issuing from inside an
+    // `if (lane == 0)` made the compiler wrap every tcgen05.mma in a per-thread R2UR/BRA.U.ANY loop); one
+    // elected lane executes the TMA / MMA / commit instructions.
+    const bool leader = elect_one();
+    if (warp == 10) {
+      if (leader) {
+        mbar_arrive_expect_tx(q_full, 2 * ATT_TILE_BYTES);
+        tma_load_3d(sQ[0], &tmap_qkv, q_full, h * ATT_DH, q0, b);
+        tma_load_3d(sQ[1], &tmap_qkv, q_full, h * ATT_DH, q0 + 128, b);
+      }
+      __syncwarp();
+      for (int j = 0; j < n_tiles; ++j) {
+        // tile j reuses the stage of tile j - STAGES once both warpgroups' PV of that tile have completed
+        if (j >= ATT_KV_STAGES) mbar_wait(&kv_empty[j % ATT_KV_STAGES], ((j / ATT_KV_STAGES) - 1) & 1);
+        if (leader) load_kv(j);
+        __syncwarp();
+      }
+    } else if (warp < 10) {
+      const int wi = warp - 8;
+      mbar_wait(q_full, 0);
+      mbar_wait(&kv_full[0], 0);
+      tc_fence_after();
+      if (leader) issue_s(wi, 0);
+      __syncwarp();
+      for (int j = 0; j < n_tiles; ++j) {
+        if (j + 1 < n_tiles) {
+          // S(j+1) as soon as the warpgroup has pulled S(j) into registers: it is ready long before softmax(j) ends
+          mbar_wait(&kv_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
+          mbar_wait(&s_free[wi], j & 1);
+          tc_fence_after();
+          if (leader) issue_s(wi, j + 1);
+          __syncwarp();
+        }
+        mbar_wait(&p_full[wi], j & 1);   // P(j) published by the 4 softmax warps (V(j) arrived with K(j))
+        tc_fence_after();
+        if (leader) issue_pv(wi, j);
+        __syncwarp();
+      }
     }
-    mbar_wait(q_full, 0);
-    mbar_wait(&kv_full[0], 0);
-    tc_fence_after();
-    issue_s(0);
-  }
-  __syncwarp();
-
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(ATT_REGS_SOFTMAX));
+#ifdef ATT_PROFILE
+  long long t_wait = 0, t_ld = 0, t_ld2 = 0, t_max = 0, t_exp = 0, t_pub = 0, t_issue = 0, tp;
+#define TICK(acc) { const long long tn = clock64(); acc += tn - tp; tp = tn; }
+  tp = clock64();
+  const long long t_begin = tp;
+#else
+#define TICK(acc)
+#endif
   float m_used = -INFINITY, l = 0.f;
-  const uint32_t p_row_addr = smem_u32(sP[w]) + (r >> 3) * 1024 + (r & 7) * 128;
-  const int rx = r & 7;
   for (int j = 0; j < n_tiles; ++j) {
     const int n_valid = min(ATT_BK, T - j * ATT_BK);
     mbar_wait(&s_full[w], j & 1);
     tc_fence_after();
+    TICK(t_wait)
     uint32_t s[128];
     tmem_ld_32x32b_x128(tmem_s, s);
     tmem_ld_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s_free[w]);   // S columns may be overwritten by S(j+1) from now on
+    TICK(t_ld)
     if (n_valid != ATT_BK) {   // last key tile: masked keys get -inf, so exp2 gives exactly 0 below
 #pragma unroll
       for (int i = 0; i < 128; ++i)
         if (i >= n_valid) s[i] = 0xff800000u;
     }
-    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // 4 independent chains
+    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // 4 independent FMNMX3 chains
 #pragma unroll
-    for (int i = 0; i < 128; i += 4) {
-      mx4[0] = fmaxf(mx4[0], __uint_as_float(s[i]));
-      mx4[1] = fmaxf(mx4[1], __uint_as_float(s[i + 1]));
-      mx4[2] = fmaxf(mx4[2], __uint_as_float(s[i + 2]));
-      mx4[3] = fmaxf(mx4[3], __uint_as_float(s[i + 3]));
+    for (int i = 0; i < 128; i += 8) {
+      mx4[0] = max3(mx4[0], __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+      mx4[1] = max3(mx4[1], __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
+      mx4[2] = max3(mx4[2], __uint_as_float(s[i + 4]), __uint_as_float(s[i + 5]));
+      mx4[3] = max3(mx4[3], __uint_as_float(s[i + 6]), __uint_as_float(s[i + 7]));
     }
     const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
     // lazy rescale (warp-uniform, because the TMEM round trip is warp-collective)
@@ -220,44 +314,57 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
       m_used = m_new;
     }
     const float mb = m_used * scale_log2;
-    float rs4[4] = {0.f, 0.f, 0.f, 0.f};
+    TICK(t_ld2)
+    // scale, subtract the running max and sum in packed fp32 pairs (FFMA2 / FADD2). B200's MUFU does 16
+    // ex2 per clock per SM against 8192 tensor flops, so at head dim 64 the exponentials, not the MMAs, are
+    // the floor (2048 clk per key tile for both query tiles); a share of them is evaluated on the FMA pipe
+    // instead (att_exp2_poly, see above).
+    const uint64_t sc2 = pack_f32x2(scale_log2, scale_log2), nmb2 = pack_f32x2(-mb, -mb);
+    uint64_t rs2[4] = {0ull, 0ull, 0ull, 0ull};
+    uint32_t pk[64];
 #pragma unroll
-    for (int c8 = 0; c8 < 16; ++c8) {   // 16 chunks of 8 keys = one 16-byte store each
-      uint32_t pk[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float p0 = ex2_approx(fmaf(__uint_as_float(s[c8 * 8 + 2 * e]), scale_log2, -mb));
-        const float p1 = ex2_approx(fmaf(__uint_as_float(s[c8 * 8 + 2 * e + 1]), scale_log2, -mb));
-        rs4[e] += p0 + p1;
-        __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-        pk[e] = *reinterpret_cast<uint32_t*>(&hh);
+    for (int i = 0; i < 64; ++i) {
+      const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nmb2);
+      float p0, p1;
+      if (att_poly_pair(i)) {
+        att_exp2_poly(x2, p0, p1);
+      } else {
+        float x0, x1;
+        unpack_f32x2(x2, x0, x1);
+        p0 = ex2_approx(x0);
+        p1 = ex2_approx(x1);
       }
-      // K-major 128B-swizzled P tile: 64-key block (c8 >> 3), 16-byte chunk (c8 & 7) XOR (row & 7)
-      st_shared_v4(p_row_addr + (c8 >> 3) * ATT_TILE_BYTES + ((((c8 & 7) ^ rx)) << 4), pk[0], pk[1], pk[2], pk[3]);
+      rs2[i & 3] = add_f32x2(rs2[i & 3], pack_f32x2(p0, p1));
+      __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+      pk[i] = *reinterpret_cast<uint32_t*>(&hh);
     }
-    l += (rs4[0] + rs4[1]) + (rs4[2] + rs4[3]);
-    fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+    {
+      float a0, a1;
+      unpack_f32x2(add_f32x2(add_f32x2(rs2[0], rs2[1]), add_f32x2(rs2[2], rs2[3])), a0, a1);
+      l += a0 + a1;
+    }
+    TICK(t_max)
+    // P_w is single-buffered: the tensor core must have finished reading P(j-1) before it is overwritten. PV(j-1)
+    // was issued when P(j-1) was published; waiting only here, with the exponentials already in registers,
+    // hides its latency behind the MUFU work.
+    if (j > 0) mbar_wait(&o_ready[w], (j - 1) & 1);
+    tmem_st_32x32b_x32(tmem_p, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
+    tmem_st_32x32b_x32(tmem_p + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
+    tmem_st_wait();
+    TICK(t_exp)
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(&p_full[w]);
-    if (issuer) {
-      // this warpgroup's MMAs for the tile: O_w += P_w V_j, then S_w for the next key tile
-      mbar_wait(&p_full[w], j & 1);
-      tc_fence_after();
-      issue_pv(j);
-      if (j + 1 < n_tiles) {
-        mbar_wait(&kv_full[(j + 1) % ATT_KV_STAGES], ((j + 1) / ATT_KV_STAGES) & 1);
-        tc_fence_after();
-        issue_s(j + 1);
-      }
-      // warpgroup 0 also keeps the K/V ring full: tile j+2 goes into the stage tile j-1 used
-      if (w == 0 && j >= 1 && j + 2 < n_tiles) {
-        mbar_wait(&kv_empty[(j - 1) % ATT_KV_STAGES], ((j - 1) / ATT_KV_STAGES) & 1);
-        load_kv(j + 2);
-      }
-    }
+    TICK(t_pub)
     __syncwarp();
+    TICK(t_issue)
   }
+#ifdef ATT_PROFILE
+  if (blockIdx.x == 1 && blockIdx.y == 3 && blockIdx.z == 5 && lane == 0) {
+    long long* dp = att_dbg + warp * 8;
+    dp[0] = t_wait; dp[1] = t_ld; dp[2] = t_ld2; dp[3] = t_max; dp[4] = t_exp; dp[5] = t_pub + t_issue; dp[6] = clock64() - t_begin; dp[7] = n_tiles;
+  }
+#endif
   // ---- epilogue: O / l
   mbar_wait(&o_ready[w], (n_tiles - 1) & 1);
   tc_fence_after();
@@ -284,12 +391,22 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
       }
     }
   }
+#ifdef ATT_PROFILE
+  if (blockIdx.x == 1 && blockIdx.y == 3 && blockIdx.z == 5 && threadIdx.x == 0) {
+    att_dbg2[0] = t_begin - t_entry;          // prologue: barrier init, TMEM alloc, first loads
+    att_dbg2[1] = clock64() - t_begin;        // main loop + epilogue
+  }
+#endif
+  }  // softmax warps
   tc_fence_before();
   __syncthreads();
   if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+#ifdef ATT_PROFILE
+  if (blockIdx.x == 1 && blockIdx.y == 3 && blockIdx.z == 5 && threadIdx.x == 0) att_dbg2[2] = clock64() - t_entry;
+#endif
 }
 
 int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int T, int n_heads, cudaStream_t stream) {
@@ -315,6 +432,13 @@ int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int
 }  // namespace janus
 
 using namespace janus;
+
+#ifdef ATT_PROFILE
+extern "C" int32_t janus_debug_att_profile(long long* host_out) {
+  if (cudaMemcpyFromSymbol(host_out, janus::att_dbg, sizeof(long long) * 64) != cudaSuccess) return -1;
+  return cudaMemcpyFromSymbol(host_out + 64, janus::att_dbg2, sizeof(long long) * 8) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 extern "C" int32_t janus_attention_enc_bf16(const void* qkv, void* out, int32_t n_batch, int32_t T, int32_t n_heads,
                                             void* stream) {

@@ -76,44 +76,51 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.n_tiles;
-        const int mt = tile / p.n_tiles;
-        const int b = mt / p.m_tiles_per_batch;
-        const int m_tile = mt % p.m_tiles_per_batch;
-        for (int kt = 0; kt < p.k_tiles; ++kt) {
-          mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * S::STAGE_BYTES;
-          uint8_t* sb = sa + S::A_BYTES;
+    // The whole warp walks the loops (convergent code keeps coordinates and descriptors in uniform registers);
+    // one elected lane executes the TMA instructions.
+    const bool leader = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      const int n_tile = tile % p.n_tiles;
+      const int mt = tile / p.n_tiles;
+      const int b = mt / p.m_tiles_per_batch;
+      const int m_tile = mt % p.m_tiles_per_batch;
+      for (int kt = 0; kt < p.k_tiles; ++kt) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * S::STAGE_BYTES;
+        uint8_t* sb = sa + S::A_BYTES;
+        if (leader) {
           mbar_arrive_expect_tx(&full[stage], S::STAGE_BYTES);
           tma_load_3d(sa, &tmap_a, &full[stage], kt * GEMM_BK, m_tile * GEMM_BM, b);
           tma_load_2d(sb, &tmap_b, &full[stage], kt * GEMM_BK, n_tile * BN);
-          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
-      int stage = 0;
-      uint32_t phase = 0;
-      int local = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++local) {
-        const int as = local & 1;
-        const uint32_t aphase = (local >> 1) & 1;
-        mbar_wait(&tmem_empty[as], aphase ^ 1);
+    // Convergent as well: issuing from inside `if (lane == 0)` made the compiler wrap every tcgen05.mma in a
+    // per-thread R2UR / BRA.U.ANY loop.
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int local = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++local) {
+      const int as = local & 1;
+      const uint32_t aphase = (local >> 1) & 1;
+      mbar_wait(&tmem_empty[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kt = 0; kt < p.k_tiles; ++kt) {
+        mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kt = 0; kt < p.k_tiles; ++kt) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * S::STAGE_BYTES);
-          const uint64_t da = umma_smem_desc_sw128(sa);
-          const uint64_t db = umma_smem_desc_sw128(sa + S::A_BYTES);
+        const uint32_t sa = smem_u32(smem + stage * S::STAGE_BYTES);
+        const uint64_t da = umma_smem_desc_sw128(sa);
+        const uint64_t db = umma_smem_desc_sw128(sa + S::A_BYTES);
+        if (leader) {
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k) {
             // +32 bytes (16 bf16) along K inside the 128B swizzle atom = +2 in the >>4 address field
@@ -121,8 +128,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           }
           umma_commit(&empty[stage]);
           if (kt == p.k_tiles - 1) umma_commit(&tmem_full[as]);
-          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else {
