@@ -81,8 +81,7 @@ def main() -> None:
         pcm.copy_(host[k], non_blocking=True)
         out = enc.prosody.run(pcm, plan, state_in=state, want_state=True, out=pros_out)
         state.copy_(out["state"])                      # carried to the session's next chunk
-        enc.encode_lane_windows(pcm, offs, lens)
-        ses.cross_kv(enc.enc_out)
+        ses.cross_kv(enc.encode_lane_windows(pcm, offs, lens, out=ses.enc_target()))
         ses.reset()
         ses.run_steps()
         tok_host.copy_(ses.tokens[:, ses.n_prompt:], non_blocking=True)

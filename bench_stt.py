@@ -173,11 +173,13 @@ def run_gpu_stt(args) -> None:
     for j in range(enc.lanes_per_call):
         enc.prosody.run(x[j * lb * N:(j + 1) * lb * N], plan, out=enc.lanes[j].pros_out[ll])
     ev[1].record()
+    enc_bufs = []
     for j in range(enc.lanes_per_call):
-        enc.encode_lane_windows(x[j * lb * N:(j + 1) * lb * N], offs, lens)
+        enc_bufs.append(enc.encode_lane_windows(x[j * lb * N:(j + 1) * lb * N], offs, lens,
+                                                out=enc.lanes[j].session.enc_target()))
     ev[2].record()
     for j in range(enc.lanes_per_call):
-        enc.lanes[j].session.cross_kv(enc.enc_out)
+        enc.lanes[j].session.cross_kv(enc_bufs[j])   # latent sessions: nothing to do (they read the encoder states)
     ev[3].record()
     for j in range(enc.lanes_per_call):
         enc.lanes[j].session.reset()
@@ -208,14 +210,20 @@ def run_gpu_stt(args) -> None:
     d = enc.dims
     stream = torch.cuda.current_stream(dev)
     k_ms = []
+    latent = ses.latent
     for rep in range(4):
         a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
         for ln in enc.lanes[:enc.lanes_per_call]:
             s_ = ln.session
             for l in range(d.n_text_layer):
-                _abi.call("janus_dec_cross_attn_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(), s_.cross_v[l].data_ptr(),
-                          s_.att.data_ptr(), lb, d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld, stream.cuda_stream)
+                if latent:
+                    _abi.call("janus_dec_xlat_bf16", s_.qlat.data_ptr(), s_.enc_buf.data_ptr(), s_.zlat.data_ptr(), lb,
+                              d.n_audio_ctx, d.n_text_state, d.n_text_head, stream.cuda_stream)
+                else:
+                    _abi.call("janus_dec_cross_attn_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(),
+                              s_.cross_v[l].data_ptr(), s_.att.data_ptr(), lb, d.n_text_head, d.n_audio_ctx,
+                              enc.whisper.kv_ld, stream.cuda_stream)
         b_.record(stream)
         torch.cuda.synchronize()
         if rep:
@@ -276,7 +284,10 @@ def run_gpu_stt(args) -> None:
             hbm_peak, tf_peak, peak_src = 6650.0, 1400.0, "fallback (B200_PROFILING.md)"
         H, T, kv_ld = d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld
         # algorithmic bytes of one cross-attention launch: K and V of every (stream, head) once, q in, out out
-        alg_bytes = lb * H * (2 * T * 64 * 2) + 2 * lb * d.n_text_state * 2
+        if latent:   # the encoder states of every window once, absorbed queries (16 rows) in, z out
+            alg_bytes = lb * T * d.n_text_state * 2 + lb * (16 + H) * d.n_text_state * 2
+        else:
+            alg_bytes = lb * H * (2 * T * 64 * 2) + 2 * lb * d.n_text_state * 2
         achieved = alg_bytes / (xattn_ms / 1e3) / 1e9
         # encoder tensor-pipe figure for context (SURVEY 8d FLOP count)
         dd, L, Ta = d.n_audio_state, d.n_audio_layer, d.n_audio_ctx
@@ -284,7 +295,8 @@ def run_gpu_stt(args) -> None:
                          + 2 * (2 * Ta) * dd * 3 * d.n_mels + 2 * Ta * dd * 3 * dd)
         traffic = None   # dram bytes of one launch from the committed ncu --set full capture, if it is this launch shape
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_xattn_traffic.json")))
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_xlat_traffic.json" if latent else
+                                             "r01_xattn_traffic.json")))
             if (tj["lane_batch"], tj["n_heads"], tj["n_ctx"]) == (lb, H, T):
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
         except Exception:  # noqa: BLE001
@@ -298,10 +310,13 @@ def run_gpu_stt(args) -> None:
                     "packets_per_step": n_pkts * world},
             "gpu_launches": enc.kernels_per_step() * args.steps,
             "stages_ms": stages,
-            "roofline": {"kernel": "dec_cross_attn_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+            "roofline": {"kernel": "dec_xlat_kernel" if latent else "dec_cross_attn_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                         "note": "read-only stream: the peak is the measured COPY bandwidth (read+write), which a "
-                                 "pure read can exceed; 87.8% of dram peak cycles in the ncu capture",
+                         "note": ("cross-attention over the encoder states themselves (K/V projections absorbed into "
+                                  "the query / output sides): half the bytes of the K/V-cache kernel per launch"
+                                  if latent else
+                                  "read-only stream: the peak is the measured COPY bandwidth (read+write), which a "
+                                  "pure read can exceed; 87.8% of dram peak cycles in the ncu capture"),
                          "kernel_ms": xattn_ms, "algorithmic_bytes_per_launch": alg_bytes,
                          "launches_per_step": d.n_text_layer * ses.n_steps * enc.lanes_per_call,
                          "encoder_tensor": {"tflops": enc_flops / (stages["logmel_encoder_ms"] / 1e3) / 1e12,

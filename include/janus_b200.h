@@ -175,6 +175,11 @@ typedef struct {          /* device pointers; matrices bf16 row-major [out, in],
   const float* ln2_w; const float* ln2_b;
   const void* w_fc1;  const float* b_fc1;
   const void* w_fc2;  const float* b_fc2;
+  /* JANUS_DECODE_LATENT only (else NULL): the layer's cross-attention key projection regrouped per head,
+   * bf16 [H*d, 64] with row h*d + n = Wk[h*64 .. h*64+63][n] (so that q'_h = Wk_h^T q_h is a grouped GEMM),
+   * and its value projection bf16 [d, d] / fp32 [d] as separate per-layer tensors */
+  const void* w_ck_lat;
+  const void* w_cv;   const float* b_cv;
 } janus_dec_layer_t;
 
 typedef struct {
@@ -197,6 +202,10 @@ typedef struct {
  * barriers (dec_fused.cu) instead of one kernel per op; needs state->barrier. At most one fused decode
  * chain may be in flight per device at a time (its CTAs wait on each other). */
 #define JANUS_DECODE_FUSED 2
+/* JANUS_DECODE_LATENT: cross-attention reads the encoder states (state->enc_out) instead of per-layer K/V
+ * caches -- half the HBM bytes per step, no cross_k / cross_v at all (janus_b200/csrc/dec_xlat.cu). Needs
+ * d % 128 == 0, d <= 768, the w_ck_lat / w_cv / b_cv layer weights and state->enc_out / qlat / zlat. */
+#define JANUS_DECODE_LATENT 4
 
 typedef struct {
   int32_t batch, max_len, n_prompt;    /* max_len = n_prompt + max_new_tokens */
@@ -213,11 +222,14 @@ typedef struct {
   uint8_t* done;                       /* [batch] */
   int32_t* n_done;                     /* device scalar */
   void* self_k; void* self_v;          /* bf16 [L, batch, H, self_ld, 64] */
-  const void* cross_k;                 /* bf16 [L, batch, H, 64, kv_ld]  (keys contiguous) */
-  const void* cross_v;                 /* bf16 [L, batch, H, n_ctx, 64] */
+  const void* cross_k;                 /* bf16 [L, batch, H, 64, kv_ld]  (keys contiguous); NULL with JANUS_DECODE_LATENT */
+  const void* cross_v;                 /* bf16 [L, batch, H, n_ctx, 64];                   NULL with JANUS_DECODE_LATENT */
   void* x; void* xn; void* qkv; void* att; void* q; void* ff;  /* bf16 [batch, d|d|3d|d|d|4d] */
   float* logits;                       /* fp32 [batch, n_vocab_pad] */
   uint64_t* barrier;                   /* device counter for JANUS_DECODE_FUSED (zero-initialised once), else NULL */
+  const void* enc_out;                 /* JANUS_DECODE_LATENT: bf16 [batch, n_ctx, d] encoder states, else NULL */
+  void* qlat;                          /* JANUS_DECODE_LATENT: bf16 [batch, 16, d], zero-initialised once */
+  void* zlat;                          /* JANUS_DECODE_LATENT: bf16 [batch, H, d] */
 } janus_decode_state_t;
 
 /* Skinny linear layer of the decode step: out[r, n] = act(sum_k A[r,k] W[n,k] + bias[n]) (+ residual[r,n]),
@@ -230,6 +242,12 @@ int32_t janus_dec_linear_bf16(const void* A, int32_t lda, const void* W, const f
  * cross_v bf16 [batch, n_heads, n_ctx, 64]; out bf16 [batch, 64*n_heads]. */
 int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
                                   int32_t batch, int32_t n_heads, int32_t n_ctx, int32_t kv_ld, void* stream);
+/* Decode-time cross-attention over the encoder states themselves ("latent" form, K/V projections absorbed
+ * into the query and output sides -- janus_b200/csrc/dec_xlat.cu): qlat bf16 [n_windows, 16, d] (absorbed
+ * queries Wk_h^T q_h, rows >= n_heads zero), enc bf16 [n_windows, n_ctx, d]; z bf16 [n_windows, n_heads, d]
+ * = softmax_t(enc . qlat_h / 8) @ enc. Needs d % 128 == 0, d <= 768, d == 64 * n_heads. */
+int32_t janus_dec_xlat_bf16(const void* qlat, const void* enc, void* z, int32_t n_windows, int32_t n_ctx, int32_t d,
+                            int32_t n_heads, void* stream);
 /* Cross-attention K/V of all decoder layers for a batch of encoder outputs (one tcgen05 GEMM whose
  * epilogue writes the two cache layouts directly). dims->n_layers/d/n_heads describe the DECODER. */
 int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,

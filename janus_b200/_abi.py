@@ -40,6 +40,7 @@ SIGNATURES = {
     "janus_whisper_encode_bf16": (_I32, [_P, _P, _P, _I32, _P, _P, _I64, _P]),
     "janus_dec_linear_bf16": (_I32, [_P, _I32, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _P]),
     "janus_dec_cross_attn_bf16": (_I32, [_P, _P, _P, _P, _I32, _I32, _I32, _I32, _P]),
+    "janus_dec_xlat_bf16": (_I32, [_P, _P, _P, _I32, _I32, _I32, _I32, _P]),
     "janus_whisper_cross_kv_bf16": (_I32, [_P, _P, _P, _I32, _P, _P, _P]),
     "janus_whisper_decode_step": (_I32, [_P, _P, _P, _P]),
     "janus_gemm_bf16": (_I32, [_P, _I64, _I64, _P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32,

@@ -71,11 +71,6 @@ __device__ __forceinline__ void tmem_ld_32x32b_x128(uint32_t taddr, uint32_t (&r
       : "memory");
 #undef R8
 }
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -88,7 +83,7 @@ __device__ __forceinline__ void tmem_st_wait() {
 // zero-filled V row). Round to nearest integer with the 1.5*2^23 trick, degree-3 minimax polynomial for
 // 2^f on [-0.5, 0.5] (max rel. error 7.5e-5 = 2^-13.7, far inside bf16's 2^-9), exponent added to the bits.
 #ifndef ATT_POLY_MODE
-#define ATT_POLY_MODE 2
+#define ATT_POLY_MODE 1
 #endif
 __device__ __forceinline__ constexpr bool att_poly_pair(int i) {   // i = pair index 0..63 within the key tile
   return ATT_POLY_MODE == 0 ? false

@@ -474,6 +474,10 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   JANUS_CHECK_ARG(w->n_text_ctx <= 512, "decode_step: n_text_ctx must be <= 512");
   const bool light = (s->flags & JANUS_DECODE_LIGHT) != 0;
   const bool fused = (s->flags & JANUS_DECODE_FUSED) != 0;
+  const bool latent = (s->flags & JANUS_DECODE_LATENT) != 0;
+  JANUS_CHECK_ARG(!latent || (!fused && !light && s->enc_out && s->qlat && s->zlat),
+                  "decode_step: JANUS_DECODE_LATENT needs enc_out / qlat / zlat and excludes LIGHT / FUSED");
+  JANUS_CHECK_ARG(latent || (s->cross_k && s->cross_v), "decode_step: cross_k / cross_v missing");
   JANUS_CHECK_ARG(!fused || s->barrier, "decode_step: JANUS_DECODE_FUSED needs state->barrier");
   JANUS_CHECK_ARG(!light || s->batch <= 64, "decode_step: JANUS_DECODE_LIGHT needs batch <= 64 (got %d)", s->batch);
   cudaStream_t st = (cudaStream_t)stream_;
@@ -552,9 +556,31 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
     if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st, light))) return rc;
+    if (latent) {
+      JANUS_CHECK_ARG(L.w_ck_lat && L.w_cv && L.b_cv, "decode_step: layer %d has no latent cross-attention weights", l);
+      __nv_bfloat16* qlat = static_cast<__nv_bfloat16*>(s->qlat);
+      __nv_bfloat16* zlat = static_cast<__nv_bfloat16*>(s->zlat);
+      {   // absorbed queries: qlat[b, h, :] = q[b, h*64 .. h*64+63] . Wk_h   (grouped over heads, K = 64)
+        GemmParams g = {};
+        g.M_per_batch = B; g.n_batch = H; g.N = d; g.K = DH;
+        g.out = qlat; g.ldc = 16LL * d; g.out_batch_stride = d;
+        g.store_mode = STORE_ROWMAJOR; g.w_batch_rows = d;
+        if ((rc = gemm_bf16(q, d, DH, static_cast<const __nv_bfloat16*>(L.w_ck_lat), DH, g, st))) return rc;
+      }
+      if ((rc = dec_xlat(qlat, static_cast<const __nv_bfloat16*>(s->enc_out), zlat, B, T, d, H, st))) return rc;
+      {   // att[b, h*64 .. h*64+63] = zlat[b, h, :] . Wv_h^T + bv_h   (grouped over heads, N = 64)
+        GemmParams g = {};
+        g.M_per_batch = B; g.n_batch = H; g.N = DH; g.K = d;
+        g.out = att; g.ldc = d; g.out_batch_stride = DH;
+        g.store_mode = STORE_ROWMAJOR; g.w_batch_rows = DH;
+        g.bias = L.b_cv; g.bias_batch_stride = DH;
+        if ((rc = gemm_bf16(zlat, (long long)H * d, d, static_cast<const __nv_bfloat16*>(L.w_cv), d, g, st))) return rc;
+      }
+    } else {
     JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                           static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
                           static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
+    }
     if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_fc1, L.b_fc1, nullptr, ff, B, 4 * d, ACT_GELU, 0, st, light))) return rc;

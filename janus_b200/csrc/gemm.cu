@@ -93,7 +93,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (leader) {
           mbar_arrive_expect_tx(&full[stage], S::STAGE_BYTES);
           tma_load_3d(sa, &tmap_a, &full[stage], kt * GEMM_BK, m_tile * GEMM_BM, b);
-          tma_load_2d(sb, &tmap_b, &full[stage], kt * GEMM_BK, n_tile * BN);
+          tma_load_2d(sb, &tmap_b, &full[stage], kt * GEMM_BK, n_tile * BN + b * p.w_batch_rows);
         }
         __syncwarp();
         if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
@@ -151,6 +151,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       tc_fence_after();
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
       const long long row_off = (long long)b * p.out_batch_stride + (long long)(t + p.out_row_offset) * p.ldc;
+      const float* bias = p.bias ? p.bias + (long long)b * p.bias_batch_stride : nullptr;   // grouped GEMM: per-batch bias
       if (BN >= 128 && p.store_mode == STORE_ROWMAJOR) {
         // ---- coalesced path: 64 output columns (one 128-byte line per row) at a time through the warp's
         // swizzled staging slab. A thread owns row `lane` while computing (TMEM lane = row) and the
@@ -184,15 +185,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             uint32_t r[32];
             tmem_ld_32x32b_x32(taddr + g0 + 32 * hc, r);
             float4 bb[8];
-            if (p.bias) {
+            if (bias) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i) bb[i] = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + 32 * hc) + i);
+              for (int i = 0; i < 8; ++i) bb[i] = __ldg(reinterpret_cast<const float4*>(bias + n0 + 32 * hc) + i);
             }
             tmem_ld_wait();
             float v[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-            if (p.bias) {
+            if (bias) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) {
                 v[4 * i] += bb[i].x; v[4 * i + 1] += bb[i].y; v[4 * i + 2] += bb[i].z; v[4 * i + 3] += bb[i].w;
@@ -251,10 +252,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         float v[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-        if (p.bias) {
+        if (bias) {
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + i));
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + n0 + i));
             v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
           }
         }
@@ -435,7 +436,7 @@ int gemm_bf16(const __nv_bfloat16* A, long long lda, long long a_batch_stride, c
     if (rc) return rc;
   }
   {
-    const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.N};
+    const uint64_t dims[2] = {(uint64_t)p.K, (uint64_t)p.N + (uint64_t)(p.n_batch - 1) * p.w_batch_rows};
     const uint64_t str[1] = {(uint64_t)ldw * 2};
     const uint32_t box[2] = {GEMM_BK, (uint32_t)BN};
     int rc = make_tmap_bf16(&tb, W, 2, dims, str, box);

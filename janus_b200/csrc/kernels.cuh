@@ -24,6 +24,9 @@ struct GemmParams {
   __nv_bfloat16* kv_v;
   int kv_d, kv_heads, kv_ld;
   int bn_max;  // 0 = auto; otherwise cap the N tile (skinny-M decode GEMMs want many small tiles)
+  // grouped GEMM: batch b multiplies by W rows [b * w_batch_rows, b * w_batch_rows + N) and adds
+  // bias[b * bias_batch_stride + n]; 0 = every batch shares W / bias
+  int w_batch_rows, bias_batch_stride;
 };
 
 int gemm_bf16(const __nv_bfloat16* A, long long lda, long long a_batch_stride, const __nv_bfloat16* W,
@@ -32,6 +35,9 @@ int layernorm_bf16(const __nv_bfloat16* x, const float* w, const float* b, __nv_
                    long long ldx, long long ldy, cudaStream_t stream, bool pdl = false);
 int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int T, int n_heads, cudaStream_t stream);
 int num_sms();
+// latent cross-attention (dec_xlat.cu): qlat [n, 16, d] absorbed queries, enc [n, T, d] encoder states -> z [n, H, d]
+int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16* z, int n_windows, int T, int d,
+             int n_heads, cudaStream_t stream);
 int dec_linear(const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, const float* bias,
                const __nv_bfloat16* residual, void* out, int rows, int N, int K, int act, int out_f32,
                cudaStream_t stream, bool pdl = false);

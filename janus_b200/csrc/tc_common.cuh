@@ -70,6 +70,11 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 // Blackwell packed fp32 pairs (FFMA2 / FADD2) and 3-input max (FMNMX3): half the issue slots of the scalar forms
 __device__ __forceinline__ float max3(float a, float b, float c) {
   float d;

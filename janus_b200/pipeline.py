@@ -146,7 +146,9 @@ class SemanticEncoder:
             self.mel_pad = torch.empty((ec, 2 * d.n_audio_ctx + 2, d.n_mels), dtype=torch.bfloat16, device=self.device)
             self.mel_scratch = torch.empty((ec, self.whisper.frontend.frames_alloc, d.n_mels), dtype=torch.float32,
                                            device=self.device)
-            self.enc_out = torch.empty((lb, d.n_audio_ctx, d.n_audio_state), dtype=torch.bfloat16, device=self.device)
+            # latent decode sessions own their encoder-state buffer (they read it during the whole decode)
+            self.enc_out = None if self.lanes[0].session.latent else \
+                torch.empty((lb, d.n_audio_ctx, d.n_audio_state), dtype=torch.bfloat16, device=self.device)
             self.max_new = self.lanes[0].session.max_new
             self.result_slots = -(-self.n_lanes // self.lanes_per_call) + 1
             self._results = [(torch.zeros((batch, self.max_new), dtype=torch.int32, device=self.device),
@@ -185,17 +187,20 @@ class SemanticEncoder:
             out = lane.pros_out[lengths] = self.prosody.alloc_outputs(plan)
         lane.cur_pros = out
         self.prosody.run(pcm, plan, out=out)
-        self.encode_lane_windows(pcm, offs, lens)
-        lane.session.cross_kv(self.enc_out)
+        enc = self.encode_lane_windows(pcm, offs, lens, out=lane.session.enc_target())
+        lane.session.cross_kv(enc)
 
-    def encode_lane_windows(self, pcm: torch.Tensor, offs: torch.Tensor, lens: torch.Tensor) -> torch.Tensor:
-        """K1 + K2 over one lane's windows in encoder micro-batches; fills self.enc_out [lane_batch, n_ctx, d]."""
+    def encode_lane_windows(self, pcm: torch.Tensor, offs: torch.Tensor, lens: torch.Tensor,
+                            out: torch.Tensor | None = None) -> torch.Tensor:
+        """K1 + K2 over one lane's windows in encoder micro-batches; fills `out` (a latent decode session's own
+        encoder-state buffer) or the shared self.enc_out [lane_batch, n_ctx, d]."""
+        enc_out = self.enc_out if out is None else out
         for c0 in range(0, self.lane_batch, self.enc_chunk):
             n = min(self.enc_chunk, self.lane_batch - c0)
             self.whisper.frontend(pcm, offs[c0:c0 + n], lens[c0:c0 + n], decim=self.decim, scratch=self.mel_scratch[:n],
                                   out_bf16=self.mel_pad[:n])
-            self.whisper.encode(self.mel_pad[:n], out=self.enc_out[c0:c0 + n])
-        return self.enc_out
+            self.whisper.encode(self.mel_pad[:n], out=enc_out[c0:c0 + n])
+        return enc_out
 
     def encode_device(self, pcm: torch.Tensor, lengths, host_pcm: torch.Tensor | None = None) -> EncodeResult:
         """pcm: float32 device tensor holding the `batch` windows concatenated (source-rate samples);

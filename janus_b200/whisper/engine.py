@@ -112,7 +112,7 @@ class WhisperEngine:
 class DecLayerStruct(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("ln1_w", "ln1_b", "w_qkv", "b_qkv", "w_o", "b_o", "lnc_w", "lnc_b",
                                           "w_cq", "b_cq", "w_co", "b_co", "ln2_w", "ln2_b", "w_fc1", "b_fc1",
-                                          "w_fc2", "b_fc2")]
+                                          "w_fc2", "b_fc2", "w_ck_lat", "w_cv", "b_cv")]
 
 
 class DecWeightsStruct(C.Structure):
@@ -127,7 +127,7 @@ class DecodeStateStruct(C.Structure):
                 ("self_ld", C.c_int32), ("reserved0", C.c_int32)] + \
                [(n, C.c_void_p) for n in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done",
                                           "n_done", "self_k", "self_v", "cross_k", "cross_v", "x", "xn", "qkv",
-                                          "att", "q", "ff", "logits", "barrier")]
+                                          "att", "q", "ff", "logits", "barrier", "enc_out", "qlat", "zlat")]
 
 
 def _pack_decoder(self, W) -> None:
@@ -135,6 +135,8 @@ def _pack_decoder(self, W) -> None:
     n, L = d.n_text_state, d.n_text_layer
     self.c_dec_dims = DimsStruct(d.n_mels, d.n_audio_ctx, n, d.n_text_head, L)
     self.dec_layers = (DecLayerStruct * L)()
+    # latent cross-attention (dec_xlat.cu) holds one 128-key tile of encoder states in shared memory: d <= 768
+    self.latent_ok = n % 128 == 0 and n <= 768 and n == 64 * d.n_text_head and d.n_audio_state == n
     ckv_w, ckv_b = [], []
     for i in range(L):
         p = f"dec.l{i}"
@@ -150,6 +152,12 @@ def _pack_decoder(self, W) -> None:
         S.ln2_w, S.ln2_b = self._f32(W[p + ".mlp_ln.w"]).data_ptr(), self._f32(W[p + ".mlp_ln.b"]).data_ptr()
         S.w_fc1, S.b_fc1 = self._bf16(W[p + ".mlp.fc1.w"]).data_ptr(), self._f32(W[p + ".mlp.fc1.b"]).data_ptr()
         S.w_fc2, S.b_fc2 = self._bf16(W[p + ".mlp.fc2.w"]).data_ptr(), self._f32(W[p + ".mlp.fc2.b"]).data_ptr()
+        if self.latent_ok:   # JANUS_DECODE_LATENT weights: Wk regrouped per head [H*d, 64], Wv / bv per layer
+            H = d.n_text_head
+            S.w_ck_lat = self._bf16(W[p + ".cross.k.w"].view(H, 64, n).permute(0, 2, 1).reshape(H * n, 64)
+                                    .contiguous()).data_ptr()
+            S.w_cv = self._bf16(W[p + ".cross.v.w"]).data_ptr()
+            S.b_cv = self._f32(W[p + ".cross.v.b"]).data_ptr()
         ckv_w += [W[p + ".cross.k.w"], W[p + ".cross.v.w"]]
         ckv_b += [torch.zeros(n), W[p + ".cross.v.b"]]
     dw = DecWeightsStruct()
@@ -181,9 +189,13 @@ class DecodeSession:
 
     DECODE_LIGHT = 1   # JANUS_DECODE_LIGHT
     DECODE_FUSED = 2   # JANUS_DECODE_FUSED
+    DECODE_LATENT = 4  # JANUS_DECODE_LATENT
+    LATENT_MIN_BATCH = 128   # the latent kernel runs one CTA per window: below ~one window per SM the K/V kernel
+                             # (one CTA per window and head) fills the machine better
 
     def __init__(self, engine: WhisperEngine, batch: int, max_new_tokens: int, use_graph: bool = True,
-                 light: bool = False, steps_per_graph: int = 1, fused: bool = False) -> None:
+                 light: bool = False, steps_per_graph: int = 1, fused: bool = False,
+                 latent: bool | None = None) -> None:
         if not hasattr(engine, "dec_weights"):
             raise RuntimeError("engine was built without decoder weights")
         self.eng, self.B = engine, batch
@@ -206,8 +218,22 @@ class DecodeSession:
         self.self_ld = min(d.n_text_ctx, -(-self.max_len // 8) * 8)   # cache only the positions this session can reach
         self.self_k = torch.zeros((L, B, H, self.self_ld, 64), **bf)
         self.self_v = torch.zeros((L, B, H, self.self_ld, 64), **bf)
-        self.cross_k = torch.zeros((L, B, H, 64, engine.kv_ld), **bf)
-        self.cross_v = torch.zeros((L, B, H, d.n_audio_ctx, 64), **bf)
+        if latent is None:
+            latent = engine.latent_ok and not light and not fused and B >= self.LATENT_MIN_BATCH
+        if latent and not engine.latent_ok:
+            raise ValueError("latent cross-attention needs d % 128 == 0 and d <= 768")
+        if latent and (light or fused):
+            raise ValueError("latent cross-attention excludes light / fused decode sessions")
+        self.latent = latent
+        if latent:
+            # cross-attention over the encoder states themselves: no per-layer K/V (2 * L times smaller)
+            self.cross_k = self.cross_v = None
+            self.enc_buf = torch.zeros((B, d.n_audio_ctx, n), **bf)
+            self.qlat = torch.zeros((B, 16, n), **bf)      # rows >= H stay zero
+            self.zlat = torch.zeros((B, H, n), **bf)
+        else:
+            self.cross_k = torch.zeros((L, B, H, 64, engine.kv_ld), **bf)
+            self.cross_v = torch.zeros((L, B, H, d.n_audio_ctx, 64), **bf)
         self.x, self.xn = torch.zeros((B, n), **bf), torch.zeros((B, n), **bf)
         self.qkv, self.att = torch.zeros((B, 3 * n), **bf), torch.zeros((B, n), **bf)
         self.q, self.ff = torch.zeros((B, n), **bf), torch.zeros((B, 4 * n), **bf)
@@ -218,13 +244,18 @@ class DecodeSession:
         s.self_ld = self.self_ld
         if light and B > 64:
             raise ValueError("light decode sessions hold at most 64 streams")
-        s.flags = (self.DECODE_LIGHT if light else 0) | (self.DECODE_FUSED if fused else 0)
+        s.flags = (self.DECODE_LIGHT if light else 0) | (self.DECODE_FUSED if fused else 0) | \
+                  (self.DECODE_LATENT if latent else 0)
         self.barrier = torch.zeros(2, dtype=torch.int64, device=dev)   # grid-barrier counter of the fused path
         s.barrier = self.barrier.data_ptr()
         self.fused = fused
         for name in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done", "n_done", "self_k",
-                     "self_v", "cross_k", "cross_v", "x", "xn", "qkv", "att", "q", "ff", "logits"):
+                     "self_v", "x", "xn", "qkv", "att", "q", "ff", "logits"):
             setattr(s, name, getattr(self, name).data_ptr())
+        if latent:
+            s.enc_out, s.qlat, s.zlat = self.enc_buf.data_ptr(), self.qlat.data_ptr(), self.zlat.data_ptr()
+        else:
+            s.cross_k, s.cross_v = self.cross_k.data_ptr(), self.cross_v.data_ptr()
         self.state = s
         self.use_graph = use_graph
         self.graph: torch.cuda.CUDAGraph | None = None
@@ -234,7 +265,7 @@ class DecodeSession:
         self.tail_graph: torch.cuda.CUDAGraph | None = None
         # embed, final LN, logits, pick, advance + 11 per layer; fused: embed, (segment + cross-attn) per layer,
         # final segment, logits, pick, advance
-        self.kernels_per_step = (1 + 2 * L + 1 + 3) if fused else (3 + 11 * L + 2 + 1)
+        self.kernels_per_step = (1 + 2 * L + 1 + 3) if fused else (3 + (13 if latent else 11) * L + 2 + 1)
 
     def _step(self) -> None:
         e = self.eng
@@ -254,9 +285,18 @@ class DecodeSession:
         self.sum_logprob.zero_()
         self.logprob.zero_()
 
+    def enc_target(self) -> torch.Tensor | None:
+        """Latent sessions read the encoder states during the whole decode: the buffer the encoder should write
+        this session's windows into (None for K/V sessions, which copy what they need in cross_kv)."""
+        return self.enc_buf if self.latent else None
+
     def cross_kv(self, enc_out: torch.Tensor) -> None:
         e = self.eng
         assert enc_out.shape[0] == self.B and enc_out.dtype == torch.bfloat16 and enc_out.is_contiguous()
+        if self.latent:
+            if enc_out.data_ptr() != self.enc_buf.data_ptr():
+                self.enc_buf.copy_(enc_out)
+            return
         _abi.call("janus_whisper_cross_kv_bf16", C.byref(e.c_dec_dims), C.byref(e.dec_weights), enc_out.data_ptr(),
                   self.B, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
                   torch.cuda.current_stream(e.device).cuda_stream)

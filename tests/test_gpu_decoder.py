@@ -33,7 +33,10 @@ def _setup(profile, seed, n_clips=3, layers=2, d=128, heads=2):
     return dims, spec, W, clips, mel, enc_ref, eng, R
 
 
-def test_teacher_forced_vs_oracle():
+@pytest.mark.parametrize("latent", [False, True])
+def test_teacher_forced_vs_oracle(latent):
+    """latent=True: cross-attention over the encoder states with absorbed K/V projections (dec_xlat.cu) -- the same
+    tolerances as the K/V-cache kernel."""
     from janus_b200.whisper.engine import DecodeSession
     dims, spec, W, clips, mel, enc_ref, eng, R = _setup("diverse", 3)
     n_new = 40
@@ -41,7 +44,8 @@ def test_teacher_forced_vs_oracle():
     # feed the ORACLE's encoder states (rounded to bf16) so this test isolates the decoder
     enc_bf16 = enc_ref.to(torch.bfloat16).cuda().contiguous()
     for use_graph in (False, True):
-        ses = DecodeSession(eng, batch=len(clips), max_new_tokens=n_new, use_graph=use_graph)
+        ses = DecodeSession(eng, batch=len(clips), max_new_tokens=n_new, use_graph=use_graph, latent=latent)
+        assert ses.latent == latent
         toks, sum_lp = ses.decode(enc_bf16, forced=ref_tok.cuda())
         torch.cuda.synchronize()
         assert torch.equal(toks.cpu().long(), ref_tok)  # forced
@@ -63,7 +67,8 @@ def test_teacher_forced_vs_oracle():
         assert ratio <= 1.0 and err.mean() <= 0.02
 
 
-def test_greedy_bit_exact_confident_end_to_end():
+@pytest.mark.parametrize("latent", [False, True])
+def test_greedy_bit_exact_confident_end_to_end(latent):
     """audio -> K1 log-mel -> K2 encoder -> cross-KV -> K3 greedy == oracle pipeline, token for token."""
     from janus_b200.whisper.engine import DecodeSession
     dims, spec, W, clips, mel, enc_ref, eng, R = _setup("confident", 3)
@@ -75,7 +80,7 @@ def test_greedy_bit_exact_confident_end_to_end():
     pcm = torch.from_numpy(np.concatenate(clips)).to(dev)
     mel_pad, _ = eng.frontend(pcm, offs.to(dev), lens.to(dev))
     enc = eng.encode(mel_pad)
-    ses = DecodeSession(eng, batch=len(clips), max_new_tokens=n_new)
+    ses = DecodeSession(eng, batch=len(clips), max_new_tokens=n_new, latent=latent)
     toks, sum_lp = ses.decode(enc)
     torch.cuda.synchronize()
     print("min oracle margin", float(margins[margins < 1e30].min()), "tokens", toks[0, :8].tolist())
@@ -189,7 +194,7 @@ def test_fused_segment_matches_per_op_path_many_rows(batch):
     g = torch.Generator().manual_seed(5)
     enc = torch.randn(batch, dims.n_audio_ctx, dims.n_audio_state, generator=g).to(torch.bfloat16).cuda()
     n_new = 12
-    a = DecodeSession(eng, batch=batch, max_new_tokens=n_new, use_graph=False)
+    a = DecodeSession(eng, batch=batch, max_new_tokens=n_new, use_graph=False, latent=False)   # same K/V kernel as fused
     ta, _ = a.decode(enc)
     b = DecodeSession(eng, batch=batch, max_new_tokens=n_new, fused=True, steps_per_graph=4)
     ta = ta.clone()
@@ -217,3 +222,33 @@ def test_long_decode_positions_past_128():
     choice = ses.choice[:, ses.n_prompt:].cpu().long()
     agree = float((choice == ref_tok).float().mean())
     assert agree > 0.97, agree
+
+
+def test_latent_session_matches_kv_session_many_windows():
+    """Whisper-small shapes, 160 windows (more than one per SM: the latent kernel's window loop and the grouped
+    absorb / value GEMMs at real sizes): teacher-forced logits of the latent session against the K/V-cache
+    session on the same encoder states. Both are bf16 pipelines that round at different places; the bound is the
+    one the K/V path itself has against the fp32 oracle."""
+    from janus_b200.whisper.config import PRESETS
+    from janus_b200.whisper.engine import DecodeSession, WhisperEngine
+    from janus_b200.whisper.weights import init_random_weights
+    dims = PRESETS["small"]
+    W = init_random_weights(dims, seed=5, profile="diverse")
+    eng = WhisperEngine(dims, W, torch.device("cuda", 0))
+    B, n_new = 160, 6
+    g = torch.Generator(device="cuda").manual_seed(11)
+    enc = torch.randn(B, dims.n_audio_ctx, dims.n_audio_state, device="cuda", generator=g).bfloat16()
+    a = DecodeSession(eng, batch=B, max_new_tokens=n_new, latent=False)
+    ta, _ = a.decode(enc)
+    torch.cuda.synchronize()
+    b = DecodeSession(eng, batch=B, max_new_tokens=n_new)
+    assert b.latent and b.cross_k is None
+    tb, _ = b.decode(enc, forced=ta)
+    torch.cuda.synchronize()
+    la, lb_ = a.logits[:, :dims.n_vocab].float(), b.logits[:, :dims.n_vocab].float()
+    err = (la - lb_).abs()
+    print(f"latent vs K/V logits: max {err.max():.4f} mean {err.mean():.5f} (std {la.std():.3f})")
+    assert err.mean() <= 0.02 and err.max() <= 0.25
+    agree = (a.choice[:, a.n_prompt:] == b.choice[:, b.n_prompt:]).float().mean().item()
+    print(f"argmax agreement {agree:.4f}")
+    assert agree >= 0.98
