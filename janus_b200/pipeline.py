@@ -82,7 +82,7 @@ class _Lane:
         self.stream = torch.cuda.Stream(dev)
         with torch.cuda.stream(self.stream):
             self.session = DecodeSession(enc.whisper, enc.lane_batch, enc.max_new_tokens, light=enc.light,
-                                         steps_per_graph=enc.steps_per_graph, fused=enc.fused)
+                                         steps_per_graph=enc.steps_per_graph, fused=enc.fused, latent=enc.latent)
             self.session._ensure_graph()
         self.stream.synchronize()
         self.ready = torch.cuda.Event()    # encoder stream -> lane: cross-KV of this lane is written
@@ -97,7 +97,8 @@ class SemanticEncoder:
 
       encoder stream   for each lane in turn: YIN/RMS prosody, log-mel, Whisper encoder (tensor-pipe
                        bound, tcgen05) and the cross-K/V projection of that lane's windows
-      lane streams     the lane's greedy decode (HBM-bound: 55 MB of cross-K/V per window and step),
+      lane streams     the lane's greedy decode (HBM-bound: 27 MB of encoder states per window and step with
+                       latent cross-attention -- lanes of >= 128 windows -- else 55 MB of cross-K/V),
                        replayed from a CUDA graph, then a copy of its tokens/tags into the result slot
 
     The decode kernels of a lane use no TMEM and < 32 KB of shared memory (JANUS_DECODE_LIGHT), so they
@@ -110,7 +111,7 @@ class SemanticEncoder:
                  device=None, seed: int = 0, weights: dict | None = None, weight_profile: str = "confident",
                  prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, lane_batch: int = 64,
                  n_lanes: int | None = None, steps_per_graph: int = 10, light: bool | None = None,
-                 fused: bool = False, enc_chunk: int = 64) -> None:
+                 fused: bool = False, enc_chunk: int = 64, latent: bool | None = None) -> None:
         self.dims = PRESETS[model] if isinstance(model, str) else model
         self.spec = tokenizer_spec(self.dims)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -125,6 +126,9 @@ class SemanticEncoder:
         if self.n_lanes < self.lanes_per_call:
             raise ValueError("n_lanes must be >= batch / lane_batch")
         self.fused = fused
+        # None: decode sessions pick latent cross-attention (over the encoder states, half the HBM bytes per
+        # step) whenever the model fits and a lane holds >= DecodeSession.LATENT_MIN_BATCH windows
+        self.latent = latent
         self.light = (self.lane_batch <= 64 and not fused) if light is None else light
         self.max_new_tokens, self.steps_per_graph = max_new_tokens, steps_per_graph
         self.decim = input_sample_rate // 16000
