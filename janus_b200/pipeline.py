@@ -129,7 +129,7 @@ class SemanticEncoder:
         # None: decode sessions pick latent cross-attention (over the encoder states, half the HBM bytes per
         # step) whenever the model fits and a lane holds >= DecodeSession.LATENT_MIN_BATCH windows
         self.latent = latent
-        self.light = (self.lane_batch <= 64 and not fused) if light is None else light
+        self.light = (self.lane_batch <= 64 and not fused and not latent) if light is None else light
         self.max_new_tokens, self.steps_per_graph = max_new_tokens, steps_per_graph
         self.decim = input_sample_rate // 16000
         assert input_sample_rate in (16000, 48000)
