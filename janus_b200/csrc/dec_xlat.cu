@@ -217,12 +217,13 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
 #pragma unroll
         for (int h = 0; h < XL_HP; ++h) {
           s[h] = valid ? __uint_as_float(sr[h]) * scale_log2 : -INFINITY;
-          mx[h] = s[h];
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-          for (int h = 0; h < XL_HP; ++h) mx[h] = fmaxf(mx[h], __shfl_xor_sync(FULL_MASK, mx[h], o));
+          // max over the warp's 32 keys with one REDUX per head: floats order like sign-magnitude integers, so
+          // flipping the magnitude bits of negatives gives a monotonic int32 key (and back with the same flip)
+          int k = __float_as_int(s[h]);
+          k ^= (k >> 31) & 0x7fffffff;
+          k = __reduce_max_sync(FULL_MASK, k);
+          k ^= (k >> 31) & 0x7fffffff;
+          mx[h] = __int_as_float(k);
         }
         float* rm = red_max + (g & 1) * 64;
         if (lane < XL_HP) {
