@@ -29,6 +29,7 @@
 //              (shuffles + one 128-thread named barrier), lazy rescale of Y in TMEM, p = 2^(s - m) to shared
 //              memory as the B operand of GEMM2. Per window: Z = Y / l as bf16.
 // S is double-buffered in TMEM so GEMM1 of tile t+1 overlaps softmax(t); TMEM use: 2 x 16 + (d / 128) x 16 columns.
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace janus {
@@ -69,6 +70,15 @@ __device__ __forceinline__ void xl_softmax_barrier() { asm volatile("bar.sync 1,
 __device__ __forceinline__ void st_shared_u16(uint32_t addr, uint16_t v) {
   asm volatile("st.shared.u16 [%0], %1;\n" ::"r"(addr), "h"(v) : "memory");
 }
+
+#ifdef XL_PROFILE   // phase timing of one CTA (build with JANUS_NVCC_EXTRA=-DXL_PROFILE, scripts/gpu_xlat_bench.py)
+__device__ long long xl_dbg[16];
+#define XL_T0 long long xl_t = clock64();
+#define XL_ACC(acc) { const long long n_ = clock64(); acc += n_ - xl_t; xl_t = n_; }
+#else
+#define XL_T0
+#define XL_ACC(acc)
+#endif
 
 __global__ void __launch_bounds__(XL_THREADS, 1)
 dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_q,
@@ -142,6 +152,18 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           }
           __syncwarp();
         }
+        // The ring holds one tile, so the loads of the next tile cannot be issued before GEMM2 releases the boxes:
+        // pull the next tile (and the next window's Q') into L2 now, so that those loads are L2 hits.
+        if (leader) {
+          int tn = t + 1, wn = w;
+          if (tn == n_tiles) { tn = 0; wn = w + gridDim.x; }
+          if (wn < n_windows) {
+            for (int kb = 0; kb < nb; ++kb) tma_prefetch_3d(&tmap_x, kb * 64, tn * XL_KEYS, wn);
+            if (tn == 0)
+              for (int kb = 0; kb < nb; ++kb) tma_prefetch_3d(&tmap_q, kb * 64, 0, wn);
+          }
+        }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
@@ -151,12 +173,19 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
     constexpr uint32_t idesc_y = umma_idesc_bf16(128, XL_HP, 1, 0);   // A = X^T: MN-major
     const uint32_t x_addr = smem_u32(sX), q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
     int g = 0, i = 0;
+#ifdef XL_PROFILE
+    long long a_box = 0, a_g1 = 0, a_p = 0, a_g2 = 0, a_box0 = 0;
+#endif
+    XL_T0
     for (int w = blockIdx.x; w < n_windows; w += gridDim.x, ++i) {
       mbar_wait(q_full, i & 1);
       for (int t = 0; t < n_tiles; ++t, ++g) {
         const uint32_t d_s = tmem_base + (g & 1) * XL_HP;
         for (int kb = 0; kb < nb; ++kb) {   // GEMM1: S[128 keys x 16 heads] += X_box[128 x 64] Q'_box[16 x 64]^T
           mbar_wait(&box_full[kb], g & 1);
+#ifdef XL_PROFILE
+          if (kb == 0) XL_ACC(a_box0) else XL_ACC(a_box)
+#endif
           tc_fence_after();
           if (leader) {
             const uint64_t da = umma_smem_desc_sw128(x_addr + kb * XL_BOX_BYTES);
@@ -165,6 +194,7 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
             for (int k = 0; k < 4; ++k) umma_f16(d_s, da + 2 * k, db + 2 * k, idesc_s, (kb | k) != 0);
           }
           __syncwarp();
+          XL_ACC(a_g1)
         }
         if (leader) {
           umma_commit(&s_full[g & 1]);
@@ -172,6 +202,7 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
         }
         __syncwarp();
         mbar_wait(p_full, g & 1);
+        XL_ACC(a_p)
         tc_fence_after();
         for (int fb = 0; fb < nfb; ++fb) {   // GEMM2: Y^T[128 features x 16 heads] += X_boxes^T[128 x 128 keys] P[128 keys x 16]
           if (leader) {
@@ -191,8 +222,12 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           if (t == n_tiles - 1) umma_commit(y_full);
         }
         __syncwarp();
+        XL_ACC(a_g2)
       }
     }
+#ifdef XL_PROFILE
+    if (blockIdx.x == 3 && lane == 0) { xl_dbg[0] = a_box0; xl_dbg[1] = a_box; xl_dbg[2] = a_g1; xl_dbg[3] = a_p; xl_dbg[4] = a_g2; xl_dbg[5] = g; }
+#endif
   } else {
     // ===================== softmax / epilogue (warps 2..5) =====================
     const int q4 = warp & 3;                 // TMEM lane quarter this warp may access
@@ -202,12 +237,17 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
     float* red_max = red;                    // [2][4][16]
     float* red_sum = red + 128;              // [4][16]
     int g = 0, i = 0;
+#ifdef XL_PROFILE
+    long long a_ws = 0, a_mx = 0, a_pp = 0, a_ep = 0;
+#endif
+    XL_T0
     for (int w = blockIdx.x; w < n_windows; w += gridDim.x, ++i) {
       float m_run[XL_HP], l_part[XL_HP];
 #pragma unroll
       for (int h = 0; h < XL_HP; ++h) { m_run[h] = -INFINITY; l_part[h] = 0.f; }
       for (int t = 0; t < n_tiles; ++t, ++g) {
         mbar_wait(&s_full[g & 1], (g >> 1) & 1);
+        XL_ACC(a_ws)
         tc_fence_after();
         uint32_t sr[XL_HP];
         tmem_ld_32x32b_x16(tmem_base + (g & 1) * XL_HP + lane_off, sr);
@@ -233,6 +273,7 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           rm[sw * XL_HP + lane] = v;
         }
         xl_softmax_barrier();
+        XL_ACC(a_mx)
         bool need = t == 0;
 #pragma unroll
         for (int h = 0; h < XL_HP; ++h) {
@@ -275,6 +316,7 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(p_full);
+        XL_ACC(a_pp)
       }
       // ---- window epilogue: Z[w, h, :] = Y[h, :] / l[h]
 #pragma unroll
@@ -305,7 +347,11 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           if (h < n_heads) zp[(long long)h * d] = __float2bfloat16_rn(__uint_as_float(y[h]) * inv[h]);
       }
       xl_softmax_barrier();   // red_sum is rewritten by the next window's epilogue only after everyone read it
+      XL_ACC(a_ep)
     }
+#ifdef XL_PROFILE
+    if (blockIdx.x == 3 && threadIdx.x == 64) { xl_dbg[8] = a_ws; xl_dbg[9] = a_mx; xl_dbg[10] = a_pp; xl_dbg[11] = a_ep; xl_dbg[12] = g; }
+#endif
   }
   tc_fence_before();
   __syncthreads();
@@ -341,7 +387,14 @@ int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16*
     JANUS_CUDA(cudaFuncSetAttribute(dec_xlat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_bytes = smem;
   }
-  const int grid = n_windows < num_sms() ? n_windows : num_sms();
+  int max_ctas = num_sms();
+  static int cap = -1;   // JANUS_XLAT_CTAS=n caps the persistent grid (scaling experiments)
+  if (cap < 0) {
+    const char* e = getenv("JANUS_XLAT_CTAS");
+    cap = e ? atoi(e) : 0;
+  }
+  if (cap > 0 && cap < max_ctas) max_ctas = cap;
+  const int grid = n_windows < max_ctas ? n_windows : max_ctas;
   const float scale_log2 = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
   JANUS_CUDA(launch_pdl(dec_xlat_kernel, dim3(grid), dim3(XL_THREADS), smem, stream, tx, tq, z, T, d, n_heads,
                         n_windows, scale_log2));
@@ -349,6 +402,12 @@ int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16*
 }
 
 }  // namespace janus
+
+#ifdef XL_PROFILE
+extern "C" int32_t janus_debug_xlat_profile(long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, janus::xl_dbg, sizeof(long long) * 16) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 extern "C" int32_t janus_dec_xlat_bf16(const void* qlat, const void* enc, void* z, int32_t n_windows, int32_t n_ctx,
                                        int32_t d, int32_t n_heads, void* stream) {

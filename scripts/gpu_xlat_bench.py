@@ -19,3 +19,15 @@ e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 20
 byt = enc.numel() * 2 + qlat.numel() * 2 + z.numel() * 2
 print(f"dec_xlat n={n}: {ms:.3f} ms  {byt / ms / 1e6:.0f} GB/s  ({4.0 * n * T * d * 16 / ms / 1e9:.0f} TFLOP/s issued)")
+try:   # phase timing, only in a -DXL_PROFILE build
+    import ctypes
+    fn = _abi.lib().janus_debug_xlat_profile
+    buf = (ctypes.c_longlong * 16)()
+    fn.restype = ctypes.c_int32
+    assert fn(buf) == 0
+    g = max(1, buf[5])
+    print(f"MMA warp per tile: wait box0 {buf[0]/g:.0f}  wait other boxes {buf[1]/g:.0f}  gemm1 issue {buf[2]/g:.0f}  wait P {buf[3]/g:.0f}  gemm2 issue {buf[4]/g:.0f}  (tiles {g})")
+    g = max(1, buf[12])
+    print(f"softmax per tile: wait S {buf[8]/g:.0f}  ld+max+barrier {buf[9]/g:.0f}  rescale+p+publish {buf[10]/g:.0f}  epilogue/tile {buf[11]/g:.0f}")
+except AttributeError:
+    pass
