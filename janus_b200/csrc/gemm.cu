@@ -201,7 +201,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
             if (p.act == ACT_GELU) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = gelu_erf_fast(v[i]);
+              for (int i = 0; i < 32; i += 2) gelu_erf_fast2(v[i], v[i + 1]);
             }
             if (p.pos && row_ok) {
               const float* pp = p.pos + (long long)t * p.N + n0 + 32 * hc;
@@ -261,7 +261,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         if (p.act == ACT_GELU) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = gelu_erf_fast(v[i]);
+          for (int i = 0; i < 32; i += 2) gelu_erf_fast2(v[i], v[i + 1]);
         }
         if (row_ok) {
           if (p.pos) {

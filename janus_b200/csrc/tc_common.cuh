@@ -94,6 +94,11 @@ __device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   return d;
 }
+__device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
 __device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
   uint64_t d;
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
@@ -271,6 +276,33 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
   const float erfc_abs = poly * e;                       // erfc(|z|) in (0, 1]
   const float one_plus_erf = x < 0.f ? erfc_abs : 2.f - erfc_abs;
   return 0.5f * x * one_plus_erf;
+}
+
+// Two erf-GELUs at once in packed fp32 pairs (FMUL2 / FFMA2 halve the issue slots of the epilogue, which is what
+// bounds the fc1 GEMM: 8 epilogue warps against a K = 768 mainloop). Same Abramowitz-Stegun erfc as above, written
+// without the sign select:  gelu(x) = max(x, 0) - 0.5 |x| erfc(|x| / sqrt 2).
+__device__ __forceinline__ void gelu_erf_fast2(float& x0, float& x1) {
+  const float a0 = fabsf(x0), a1 = fabsf(x1);
+  const uint64_t a = pack_f32x2(a0, a1);
+  const uint64_t z = mul_f32x2(a, pack_f32x2(0.70710678118654752440f, 0.70710678118654752440f));
+  float d0, d1;
+  unpack_f32x2(fma_f32x2(z, pack_f32x2(0.3275911f, 0.3275911f), pack_f32x2(1.f, 1.f)), d0, d1);
+  float t0, t1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  const uint64_t t = pack_f32x2(t0, t1);
+  uint64_t poly = fma_f32x2(t, pack_f32x2(1.061405429f, 1.061405429f), pack_f32x2(-1.453152027f, -1.453152027f));
+  poly = fma_f32x2(poly, t, pack_f32x2(1.421413741f, 1.421413741f));
+  poly = fma_f32x2(poly, t, pack_f32x2(-0.284496736f, -0.284496736f));
+  poly = fma_f32x2(poly, t, pack_f32x2(0.254829592f, 0.254829592f));
+  poly = mul_f32x2(poly, t);
+  float g0, g1;   // -z^2 log2(e) = a^2 * (-0.5 log2 e)
+  unpack_f32x2(mul_f32x2(mul_f32x2(a, a), pack_f32x2(-0.72134752044448170368f, -0.72134752044448170368f)), g0, g1);
+  float e0, e1;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(g0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(g1));
+  const uint64_t w = mul_f32x2(mul_f32x2(a, pack_f32x2(-0.5f, -0.5f)), poly);   // -0.5 |x| t P(t)
+  unpack_f32x2(fma_f32x2(w, pack_f32x2(e0, e1), pack_f32x2(fmaxf(x0, 0.f), fmaxf(x1, 0.f))), x0, x1);
 }
 
 }  // namespace janus
