@@ -19,6 +19,7 @@
 //     the K-major 128B-swizzled UMMA layout. O stays in TMEM and accumulates across key tiles; it is
 //     rescaled (tcgen05.ld/st) only when the running max moved by more than 2^8 ("lazy rescale"),
 //     which removes the O round trip from almost every tile.
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace janus {
@@ -27,17 +28,29 @@ constexpr int ATT_BQ = 256;   // queries per CTA: two 128-row tiles, one per sof
 constexpr int ATT_BK = 128;
 constexpr int ATT_DH = 64;
 constexpr int ATT_KV_STAGES = 4;
-constexpr int ATT_SOFTMAX_THREADS = 256;  // two softmax warpgroups (one thread per query row)
+// SPLIT = threads per query row. 1: two softmax warpgroups, a thread owns a whole 128-key row of S (232 registers
+// via setmaxnreg). 2: four softmax warpgroups, a row is shared by two threads of different warps (64 keys each;
+// row max / row sum exchanged through shared memory and a 64-thread named barrier) -- four softmax warps per
+// scheduler instead of two hide the MUFU / dependent-issue latencies that bound the one-thread-per-row form.
+template <int SPLIT> struct AttCfg {
+  static constexpr int SOFTMAX_THREADS = 256 * SPLIT;
+  static constexpr int THREADS = SOFTMAX_THREADS + 128;
+  static constexpr int REGS_ISSUER = 40;
+  // launch registers: 65536 / THREADS rounded down to 8 -> 168 (384 threads) / 96 (640 threads)
+  static constexpr int REGS_SOFTMAX = SPLIT == 1 ? 232 : 104;   // 128*40 + 256*232 == 384*168;  128*40 + 512*104 <= 640*96
+  static constexpr int COLS = 128 / SPLIT;     // S columns (keys) per thread
+  static constexpr int OCOLS = 64 / SPLIT;     // O columns per thread
+};
 // + warpgroup 2: one thread of warp 8 issues every TMA load and tcgen05.mma. Registers are allocated per
 // warpgroup, so a 9th warp costs a whole warpgroup's worth: the kernel launches at 168 registers x 384 threads
 // and setmaxnreg moves the issuer warpgroup's share (it needs < 40) to the softmax warpgroups (128 fp32 scores
 // per thread live in registers).
-constexpr int ATT_THREADS = ATT_SOFTMAX_THREADS + 128;
-constexpr int ATT_REGS_ISSUER = 40;
-constexpr int ATT_REGS_SOFTMAX = 232;   // 128*40 + 256*232 == 384*168
 constexpr int ATT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: a Q, K or V tile
 // Q0 Q1 | (K V) x stages | P0 P1 (32 KB each) | barriers
-constexpr int ATT_SMEM = ATT_TILE_BYTES * (2 + 2 * ATT_KV_STAGES) + 256;
+constexpr int ATT_SMEM = ATT_TILE_BYTES * (2 + 2 * ATT_KV_STAGES) + 256 + 4096;   // tiles | barriers | row-stat exchange
+#ifndef ATT_DEFAULT_SPLIT
+#define ATT_DEFAULT_SPLIT 1
+#endif
 constexpr float ATT_RESCALE_LOG2 = 8.0f;  // lazy rescale threshold: p = exp2(.) stays below 2^8
 
 __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
@@ -111,17 +124,13 @@ __device__ __forceinline__ void att_exp2_poly(uint64_t x2, float& p0, float& p1)
   p1 = __uint_as_float(__float_as_uint(q1) + (__float_as_uint(r1) << 23));
 }
 
-#ifdef ATT_PROFILE
-__device__ long long att_dbg[8 * 8];
-__device__ long long att_dbg2[8];
-#endif
-
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+template <int SPLIT>
+__global__ void __launch_bounds__(AttCfg<SPLIT>::THREADS, 1)
 attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16* __restrict__ out, int T, int d,
                      float scale_log2) {
-#ifdef ATT_PROFILE
-  const long long t_entry = clock64();
-#endif
+  using C = AttCfg<SPLIT>;
+  constexpr int NSW = C::SOFTMAX_THREADS / 32;   // softmax warps; warps NSW / NSW+1 issue MMAs, NSW+2 runs TMA
+  constexpr int COLS = C::COLS, OCOLS = C::OCOLS;
   extern __shared__ __align__(1024) uint8_t smem[];  // 128B-swizzled tiles need 1024 B alignment
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* sQ[2] = {smem, smem + ATT_TILE_BYTES};
@@ -133,8 +142,9 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
   uint64_t* s_full = kv_empty + ATT_KV_STAGES;  // [2]
   uint64_t* p_full = s_full + 2;                // [2]
   uint64_t* o_ready = p_full + 2;               // [2]
-  uint64_t* s_free = o_ready + 2;               // [2]  all 4 warps of the warpgroup hold S(j) in registers
+  uint64_t* s_free = o_ready + 2;               // [2]  every softmax warp of the tile holds S(j) in registers
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_free + 2);
+  float* xch = reinterpret_cast<float*>(bars + 32);   // SPLIT == 2: [2 parities][2 tiles][4 quarters][2 halves][32] row stats
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -148,13 +158,13 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
     mbar_init(q_full, 1);
     for (int i = 0; i < ATT_KV_STAGES; ++i) {
       mbar_init(&kv_full[i], 1);
-      mbar_init(&kv_empty[i], 2);   // one tcgen05.commit per warpgroup
+      mbar_init(&kv_empty[i], 2);   // one tcgen05.commit per query tile
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], 4);
+      mbar_init(&p_full[i], 4 * SPLIT);
       mbar_init(&o_ready[i], 1);
-      mbar_init(&s_free[i], 4);
+      mbar_init(&s_free[i], 4 * SPLIT);
     }
     fence_mbar_init();
   }
@@ -168,12 +178,15 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
   // memory: with P in shared memory the kernel moved 256 KB per key tile through the 128 B/clk smem port
   // (Q, K, V and P operand reads, the P stores and the TMA fills) -- as long as the MUFU floor.
 
-  const int w = (warp >> 2) & 1;           // warpgroup 0 / 1 == query tile (softmax warps 0..7)
-  const int r = threadIdx.x & 127;         // row within the 128-query tile == TMEM lane
-  const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-  const uint32_t tmem_s = tmem_base + w * 128 + lane_off;
-  const uint32_t tmem_o = tmem_base + 256 + w * 64 + lane_off;
-  const uint32_t tmem_p = tmem_base + 384 + w * 64 + lane_off;
+  // softmax warp -> (query tile w, TMEM lane quarter, column half)
+  const int w = (warp / (4 * SPLIT)) & 1;
+  const int quarter = warp & 3;
+  const int half = SPLIT == 2 ? (warp >> 2) & 1 : 0;
+  const int r = quarter * 32 + lane;       // row within the 128-query tile == TMEM lane
+  const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+  const uint32_t tmem_s = tmem_base + w * 128 + half * COLS + lane_off;
+  const uint32_t tmem_o = tmem_base + 256 + w * 64 + half * OCOLS + lane_off;
+  const uint32_t tmem_p = tmem_base + 384 + w * 64 + half * (COLS / 2) + lane_off;
   constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);
   constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, 0, 1);  // B (= V) is MN-major
 
@@ -201,19 +214,16 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
     umma_commit(&kv_empty[j % ATT_KV_STAGES]);
   };
 
-  // ---- warp 8: the only thread that talks to the TMA unit and the tensor core. tcgen05.mma issue
-  // back-pressures the issuing thread while the tensor core is busy (measured: ~1800 cycles per tile
-  // when a softmax thread did the issuing), so it must not sit on the softmax critical path.
-  if (warp >= 8) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(ATT_REGS_ISSUER));
-    // Warps 8 / 9 issue the MMAs of query tile 0 / 1, warp 10 runs the K/V ring. Each is a straight sequence of
-    // blocking mbarrier waits (a suspended wait costs no issue slots, a polling loop over several barriers
-    // measured ~1700 cycles per round because it competes with the softmax warps of its scheduler), run by
-    // the whole warp so that descriptors and TMEM addresses stay in uniform registers (issuing from inside an
-    // `if (lane == 0)` made the compiler wrap every tcgen05.mma in a per-thread R2UR/BRA.U.ANY loop); one
-    // elected lane executes the TMA / MMA / commit instructions.
+  if (warp >= NSW) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REGS_ISSUER));
+    // Warps NSW / NSW+1 issue the MMAs of query tile 0 / 1, warp NSW+2 runs the K/V ring. Each is a straight
+    // sequence of blocking mbarrier waits (a suspended wait costs no issue slots; a polling loop over several
+    // barriers measured ~1700 cycles per round because it competes with the softmax warps of its scheduler), run
+    // by the whole warp so that descriptors and TMEM addresses stay in uniform registers (issuing from inside an
+    // `if (lane == 0)` made the compiler wrap every tcgen05.mma in a per-thread R2UR/BRA.U.ANY loop, ~150 cycles
+    // per MMA, on the softmax critical path); one elected lane executes the TMA / MMA / commit instructions.
     const bool leader = elect_one();
-    if (warp == 10) {
+    if (warp == NSW + 2) {
       if (leader) {
         mbar_arrive_expect_tx(q_full, 2 * ATT_TILE_BYTES);
         tma_load_3d(sQ[0], &tmap_qkv, q_full, h * ATT_DH, q0, b);
@@ -226,8 +236,8 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
         if (leader) load_kv(j);
         __syncwarp();
       }
-    } else if (warp < 10) {
-      const int wi = warp - 8;
+    } else if (warp < NSW + 2) {
+      const int wi = warp - NSW;
       mbar_wait(q_full, 0);
       mbar_wait(&kv_full[0], 0);
       tc_fence_after();
@@ -249,149 +259,143 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
       }
     }
   } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(ATT_REGS_SOFTMAX));
-#ifdef ATT_PROFILE
-  long long t_wait = 0, t_ld = 0, t_ld2 = 0, t_max = 0, t_exp = 0, t_pub = 0, t_issue = 0, tp;
-#define TICK(acc) { const long long tn = clock64(); acc += tn - tp; tp = tn; }
-  tp = clock64();
-  const long long t_begin = tp;
-#else
-#define TICK(acc)
-#endif
-  float m_used = -INFINITY, l = 0.f;
-  for (int j = 0; j < n_tiles; ++j) {
-    const int n_valid = min(ATT_BK, T - j * ATT_BK);
-    mbar_wait(&s_full[w], j & 1);
-    tc_fence_after();
-    TICK(t_wait)
-    uint32_t s[128];
-    tmem_ld_32x32b_x128(tmem_s, s);
-    tmem_ld_wait();
-    tc_fence_before();
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&s_free[w]);   // S columns may be overwritten by S(j+1) from now on
-    TICK(t_ld)
-    if (n_valid != ATT_BK) {   // last key tile: masked keys get -inf, so exp2 gives exactly 0 below
-#pragma unroll
-      for (int i = 0; i < 128; ++i)
-        if (i >= n_valid) s[i] = 0xff800000u;
-    }
-    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // 4 independent FMNMX3 chains
-#pragma unroll
-    for (int i = 0; i < 128; i += 8) {
-      mx4[0] = max3(mx4[0], __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
-      mx4[1] = max3(mx4[1], __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
-      mx4[2] = max3(mx4[2], __uint_as_float(s[i + 4]), __uint_as_float(s[i + 5]));
-      mx4[3] = max3(mx4[3], __uint_as_float(s[i + 6]), __uint_as_float(s[i + 7]));
-    }
-    const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-    // lazy rescale (warp-uniform, because the TMEM round trip is warp-collective)
-    bool need = (j == 0) || ((mx - m_used) * scale_log2 > ATT_RESCALE_LOG2);
-    need = __any_sync(FULL_MASK, need);
-    if (need) {
-      const float m_new = fmaxf(m_used, mx);
-      if (j > 0) {
-        const float alpha = ex2_approx((m_used - m_new) * scale_log2);
-        l *= alpha;
-        mbar_wait(&o_ready[w], (j - 1) & 1);   // PV(j-1) has landed in O
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t o[32];
-          tmem_ld_32x32b_x32(tmem_o + 32 * c, o);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tmem_st_32x32b_x32(tmem_o + 32 * c, o);
-        }
-        tmem_st_wait();
-      }
-      m_used = m_new;
-    }
-    const float mb = m_used * scale_log2;
-    TICK(t_ld2)
-    // scale, subtract the running max and sum in packed fp32 pairs (FFMA2 / FADD2). B200's MUFU does 16
-    // ex2 per clock per SM against 8192 tensor flops, so at head dim 64 the exponentials, not the MMAs, are
-    // the floor (2048 clk per key tile for both query tiles); a share of them is evaluated on the FMA pipe
-    // instead (att_exp2_poly, see above).
-    const uint64_t sc2 = pack_f32x2(scale_log2, scale_log2), nmb2 = pack_f32x2(-mb, -mb);
-    uint64_t rs2[4] = {0ull, 0ull, 0ull, 0ull};
-    uint32_t pk[64];
-#pragma unroll
-    for (int i = 0; i < 64; ++i) {
-      const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nmb2);
-      float p0, p1;
-      if (att_poly_pair(i)) {
-        att_exp2_poly(x2, p0, p1);
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REGS_SOFTMAX));
+    float m_used = -INFINITY, l = 0.f;
+    // the two threads of a row (SPLIT == 2) meet on a 64-thread named barrier; stats are double-buffered by tile
+    // parity, so one barrier per tile is enough (a slot is rewritten two barriers after it was read)
+    const int bar_id = 1 + w * 4 + quarter;
+    float* xch_mine = xch + ((w * 4 + quarter) * 2 + half) * 32 + lane;
+    float* xch_peer = xch + ((w * 4 + quarter) * 2 + (half ^ 1)) * 32 + lane;
+    for (int j = 0; j < n_tiles; ++j) {
+      const int n_valid = min(ATT_BK, T - j * ATT_BK) - half * COLS;   // valid keys among this thread's COLS
+      mbar_wait(&s_full[w], j & 1);
+      tc_fence_after();
+      uint32_t s[COLS];
+      if constexpr (SPLIT == 1) {
+        tmem_ld_32x32b_x128(tmem_s, *reinterpret_cast<uint32_t(*)[128]>(&s[0]));
       } else {
-        float x0, x1;
-        unpack_f32x2(x2, x0, x1);
-        p0 = ex2_approx(x0);
-        p1 = ex2_approx(x1);
+        tmem_ld_32x32b_x32(tmem_s, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+        tmem_ld_32x32b_x32(tmem_s + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
       }
-      rs2[i & 3] = add_f32x2(rs2[i & 3], pack_f32x2(p0, p1));
-      __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
-      pk[i] = *reinterpret_cast<uint32_t*>(&hh);
-    }
-    {
-      float a0, a1;
-      unpack_f32x2(add_f32x2(add_f32x2(rs2[0], rs2[1]), add_f32x2(rs2[2], rs2[3])), a0, a1);
-      l += a0 + a1;
-    }
-    TICK(t_max)
-    // P_w is single-buffered: the tensor core must have finished reading P(j-1) before it is overwritten. PV(j-1)
-    // was issued when P(j-1) was published; waiting only here, with the exponentials already in registers,
-    // hides its latency behind the MUFU work.
-    if (j > 0) mbar_wait(&o_ready[w], (j - 1) & 1);
-    tmem_st_32x32b_x32(tmem_p, *reinterpret_cast<uint32_t(*)[32]>(&pk[0]));
-    tmem_st_32x32b_x32(tmem_p + 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[32]));
-    tmem_st_wait();
-    TICK(t_exp)
-    tc_fence_before();
-    __syncwarp();
-    if (lane == 0) mbar_arrive(&p_full[w]);
-    TICK(t_pub)
-    __syncwarp();
-    TICK(t_issue)
-  }
-#ifdef ATT_PROFILE
-  if (blockIdx.x == 1 && blockIdx.y == 3 && blockIdx.z == 5 && lane == 0) {
-    long long* dp = att_dbg + warp * 8;
-    dp[0] = t_wait; dp[1] = t_ld; dp[2] = t_ld2; dp[3] = t_max; dp[4] = t_exp; dp[5] = t_pub + t_issue; dp[6] = clock64() - t_begin; dp[7] = n_tiles;
-  }
-#endif
-  // ---- epilogue: O / l
-  mbar_wait(&o_ready[w], (n_tiles - 1) & 1);
-  tc_fence_after();
-  {
-    const int t = q0 + w * 128 + r;
-    const float inv = 1.f / l;
-    __nv_bfloat16* orow = out + ((long long)b * T + t) * d + h * ATT_DH;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t o[32];
-      tmem_ld_32x32b_x32(tmem_o + 32 * c, o);
       tmem_ld_wait();
-      if (t < T) {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s_free[w]);   // S columns may be overwritten by S(j+1) from now on
+      if (n_valid < COLS) {   // last key tile: masked keys get -inf, so exp2 gives exactly 0 below
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint4 u;
-          __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&u);
+        for (int i = 0; i < COLS; ++i)
+          if (i >= n_valid) s[i] = 0xff800000u;
+      }
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // 4 independent FMNMX3 chains
 #pragma unroll
-          for (int jx = 0; jx < 4; ++jx)
-            hh[jx] = __floats2bfloat162_rn(__uint_as_float(o[i * 8 + 2 * jx]) * inv,
-                                           __uint_as_float(o[i * 8 + 2 * jx + 1]) * inv);
-          reinterpret_cast<uint4*>(orow + 32 * c)[i] = u;
+      for (int i = 0; i < COLS; i += 8) {
+        mx4[0] = max3(mx4[0], __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
+        mx4[1] = max3(mx4[1], __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
+        mx4[2] = max3(mx4[2], __uint_as_float(s[i + 4]), __uint_as_float(s[i + 5]));
+        mx4[3] = max3(mx4[3], __uint_as_float(s[i + 6]), __uint_as_float(s[i + 7]));
+      }
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      if constexpr (SPLIT == 2) {   // row max over both halves
+        xch_mine[(j & 1) * 512] = mx;
+        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+        mx = fmaxf(mx, xch_peer[(j & 1) * 512]);
+      }
+      // lazy rescale (warp-uniform, because the TMEM round trip is warp-collective; with SPLIT == 2 both warps
+      // of a row group see identical row maxima and therefore take the same decision)
+      bool need = (j == 0) || ((mx - m_used) * scale_log2 > ATT_RESCALE_LOG2);
+      need = __any_sync(FULL_MASK, need);
+      if (need) {
+        const float m_new = fmaxf(m_used, mx);
+        if (j > 0) {
+          const float alpha = ex2_approx((m_used - m_new) * scale_log2);
+          l *= alpha;
+          mbar_wait(&o_ready[w], (j - 1) & 1);   // PV(j-1) has landed in O
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < OCOLS / 32; ++c) {
+            uint32_t o[32];
+            tmem_ld_32x32b_x32(tmem_o + 32 * c, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32b_x32(tmem_o + 32 * c, o);
+          }
+          tmem_st_wait();
+        }
+        m_used = m_new;
+      }
+      const float mb = m_used * scale_log2;
+      // scale, subtract the running max and sum in packed fp32 pairs (FFMA2 / FADD2). B200's MUFU does 16
+      // ex2 per clock per SM against 8192 tensor flops, so at head dim 64 the exponentials, not the MMAs, are
+      // the floor (2048 clk per key tile for both query tiles); a share of them is evaluated on the FMA pipe
+      // instead (att_exp2_poly, see above).
+      const uint64_t sc2 = pack_f32x2(scale_log2, scale_log2), nmb2 = pack_f32x2(-mb, -mb);
+      uint64_t rs2[4] = {0ull, 0ull, 0ull, 0ull};
+      uint32_t pk[COLS / 2];
+#pragma unroll
+      for (int i = 0; i < COLS / 2; ++i) {
+        const uint64_t x2 = fma_f32x2(pack_f32x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), sc2, nmb2);
+        float p0, p1;
+        if (att_poly_pair(i)) {
+          att_exp2_poly(x2, p0, p1);
+        } else {
+          float x0, x1;
+          unpack_f32x2(x2, x0, x1);
+          p0 = ex2_approx(x0);
+          p1 = ex2_approx(x1);
+        }
+        rs2[i & 3] = add_f32x2(rs2[i & 3], pack_f32x2(p0, p1));
+        __nv_bfloat162 hh = __floats2bfloat162_rn(p0, p1);
+        pk[i] = *reinterpret_cast<uint32_t*>(&hh);
+      }
+      {
+        float a0, a1;
+        unpack_f32x2(add_f32x2(add_f32x2(rs2[0], rs2[1]), add_f32x2(rs2[2], rs2[3])), a0, a1);
+        l += a0 + a1;
+      }
+      // P_w is single-buffered: the tensor core must have finished reading P(j-1) before it is overwritten.
+      // PV(j-1) was issued when P(j-1) was published; waiting only here, with the exponentials already in
+      // registers, hides its latency behind the MUFU work.
+      if (j > 0) mbar_wait(&o_ready[w], (j - 1) & 1);
+#pragma unroll
+      for (int c = 0; c < COLS / 64; ++c)
+        tmem_st_32x32b_x32(tmem_p + 32 * c, *reinterpret_cast<uint32_t(*)[32]>(&pk[32 * c]));
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[w]);
+    }
+    // ---- epilogue: O / l
+    if constexpr (SPLIT == 2) {   // row sum over both halves (slot parity continues the tile sequence)
+      xch_mine[(n_tiles & 1) * 512] = l;
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+      l += xch_peer[(n_tiles & 1) * 512];
+    }
+    mbar_wait(&o_ready[w], (n_tiles - 1) & 1);
+    tc_fence_after();
+    {
+      const int t = q0 + w * 128 + r;
+      const float inv = 1.f / l;
+      __nv_bfloat16* orow = out + ((long long)b * T + t) * d + h * ATT_DH + half * OCOLS;
+#pragma unroll
+      for (int c = 0; c < OCOLS / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(tmem_o + 32 * c, o);
+        tmem_ld_wait();
+        if (t < T) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 u;
+            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+            for (int jx = 0; jx < 4; ++jx)
+              hh[jx] = __floats2bfloat162_rn(__uint_as_float(o[i * 8 + 2 * jx]) * inv,
+                                             __uint_as_float(o[i * 8 + 2 * jx + 1]) * inv);
+            reinterpret_cast<uint4*>(orow + 32 * c)[i] = u;
+          }
         }
       }
     }
-  }
-#ifdef ATT_PROFILE
-  if (blockIdx.x == 1 && blockIdx.y == 3 && blockIdx.z == 5 && threadIdx.x == 0) {
-    att_dbg2[0] = t_begin - t_entry;          // prologue: barrier init, TMEM alloc, first loads
-    att_dbg2[1] = clock64() - t_begin;        // main loop + epilogue
-  }
-#endif
   }  // softmax warps
   tc_fence_before();
   __syncthreads();
@@ -399,9 +403,6 @@ attention_enc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, __nv_bfloat16
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
-#ifdef ATT_PROFILE
-  if (blockIdx.x == 1 && blockIdx.y == 3 && blockIdx.z == 5 && threadIdx.x == 0) att_dbg2[2] = clock64() - t_entry;
-#endif
 }
 
 int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int T, int n_heads, cudaStream_t stream) {
@@ -412,14 +413,19 @@ int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int
   const uint32_t box[3] = {ATT_DH, 128, 1};
   int rc = make_tmap_bf16(&tm, qkv, 3, dims, str, box);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    JANUS_CUDA(cudaFuncSetAttribute(attention_enc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
-    attr_set = true;
+  static int split = 0;   // threads per query row: JANUS_ATT_SPLIT=1|2 (default ATT_DEFAULT_SPLIT)
+  if (!split) {
+    const char* e = getenv("JANUS_ATT_SPLIT");
+    split = e && atoi(e) >= 1 && atoi(e) <= 2 ? atoi(e) : ATT_DEFAULT_SPLIT;
+    JANUS_CUDA(cudaFuncSetAttribute(attention_enc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    JANUS_CUDA(cudaFuncSetAttribute(attention_enc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
   }
   const dim3 grid((T + ATT_BQ - 1) / ATT_BQ, n_heads, n_batch);
   const float scale_log2 = 0.125f * 1.4426950408889634f;  // 1/sqrt(64) * log2(e)
-  attention_enc_kernel<<<grid, ATT_THREADS, ATT_SMEM, stream>>>(tm, out, T, d, scale_log2);
+  if (split == 2)
+    attention_enc_kernel<2><<<grid, AttCfg<2>::THREADS, ATT_SMEM, stream>>>(tm, out, T, d, scale_log2);
+  else
+    attention_enc_kernel<1><<<grid, AttCfg<1>::THREADS, ATT_SMEM, stream>>>(tm, out, T, d, scale_log2);
   JANUS_LAUNCH_CHECK("attention_enc_kernel");
   return JANUS_OK;
 }
@@ -427,13 +433,6 @@ int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int
 }  // namespace janus
 
 using namespace janus;
-
-#ifdef ATT_PROFILE
-extern "C" int32_t janus_debug_att_profile(long long* host_out) {
-  if (cudaMemcpyFromSymbol(host_out, janus::att_dbg, sizeof(long long) * 64) != cudaSuccess) return -1;
-  return cudaMemcpyFromSymbol(host_out + 64, janus::att_dbg2, sizeof(long long) * 8) == cudaSuccess ? 0 : -1;
-}
-#endif
 
 extern "C" int32_t janus_attention_enc_bf16(const void* qkv, void* out, int32_t n_batch, int32_t T, int32_t n_heads,
                                             void* stream) {
