@@ -19,6 +19,9 @@
 
 namespace janus {
 
+#ifndef GEMM_EPI_PREFETCH
+#define GEMM_EPI_PREFETCH 1
+#endif
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
 constexpr int GEMM_EPI_WARPS = 8;                       // 2 per TMEM lane quarter (column halves)
@@ -37,6 +40,18 @@ struct GemmSmem {
   static constexpr int BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+#ifdef GEMM_PROFILE   // phase stamps of CTA 0 (globaltimer ns): build with JANUS_NVCC_EXTRA=-DGEMM_PROFILE
+__device__ unsigned long long gemm_dbg[8];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define GSTAMP(i) if (blockIdx.x == 0 && lane == 0) gemm_dbg[i] = gtime();
+#else
+#define GSTAMP(i)
+#endif
+
 template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -54,6 +69,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (warp == 0) { GSTAMP(0) }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -73,6 +89,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (warp == 0) { GSTAMP(1) }
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -116,6 +133,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t d_tmem = tmem_base + as * BN;
       for (int kt = 0; kt < p.k_tiles; ++kt) {
         mbar_wait(&full[stage], phase);
+#ifdef GEMM_PROFILE
+        if (local == 0 && kt == 0) { GSTAMP(2) }
+        if (local == 0 && kt == p.k_tiles - 1) { GSTAMP(3) }
+#endif
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * S::STAGE_BYTES);
         const uint64_t da = umma_smem_desc_sw128(sa);
@@ -147,11 +168,30 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       const uint32_t aphase = (local >> 1) & 1;
       const int t = m_tile * GEMM_BM + q * 32 + lane;  // row within the batch
       const bool row_ok = t < p.M_per_batch;
-      mbar_wait(&tmem_full[as], aphase);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
       const long long row_off = (long long)b * p.out_batch_stride + (long long)(t + p.out_row_offset) * p.ldc;
       const float* bias = p.bias ? p.bias + (long long)b * p.bias_batch_stride : nullptr;   // grouped GEMM: per-batch bias
+      // BN == 64 is the skinny-M (decode) configuration: one tile per CTA, so nothing hides the epilogue's
+      // dependent global loads (measured 3.4-4.5 us of a 10-11 us kernel). Request bias and residual while
+      // the mainloop is still running.
+      float4 bb_pre[8];
+      uint4 res_pre[4];
+      if constexpr (GEMM_EPI_PREFETCH && BN == 64) {
+        const int n0p = n_tile * BN + chalf * 32;
+        if (bias) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) bb_pre[i] = __ldg(reinterpret_cast<const float4*>(bias + n0p) + i);
+        }
+        if (p.residual && row_ok) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) res_pre[i] = __ldg(reinterpret_cast<const uint4*>(p.residual + row_off + n0p) + i);
+        }
+      }
+      mbar_wait(&tmem_full[as], aphase);
+#ifdef GEMM_PROFILE
+      if (local == 0 && warp == 2) { GSTAMP(4) }
+#endif
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
       if (BN >= 128 && p.store_mode == STORE_ROWMAJOR) {
         // ---- coalesced path: 64 output columns (one 128-byte line per row) at a time through the warp's
         // swizzled staging slab. A thread owns row `lane` while computing (TMEM lane = row) and the
@@ -255,7 +295,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (bias) {
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + n0 + i));
+            float4 bb;
+            if constexpr (GEMM_EPI_PREFETCH && BN == 64) bb = bb_pre[i >> 2];
+            else bb = __ldg(reinterpret_cast<const float4*>(bias + n0 + i));
             v[i] += bb.x; v[i + 1] += bb.y; v[i + 2] += bb.z; v[i + 3] += bb.w;
           }
         }
@@ -276,7 +318,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const uint4* rp = reinterpret_cast<const uint4*>(p.residual + row_off + n0);
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-              const uint4 u = __ldg(rp + i);
+              uint4 u;
+              if constexpr (GEMM_EPI_PREFETCH && BN == 64) u = res_pre[i];
+              else u = __ldg(rp + i);
               const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
@@ -332,11 +376,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   }
 
+  if (warp == 2) { GSTAMP(5) }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, S::TMEM_COLS);
+    GSTAMP(6)
   }
 }
 
@@ -448,6 +494,12 @@ int gemm_bf16(const __nv_bfloat16* A, long long lda, long long a_batch_stride, c
 }
 
 }  // namespace janus
+
+#ifdef GEMM_PROFILE
+extern "C" int32_t janus_debug_gemm_profile(unsigned long long* host_out) {
+  return cudaMemcpyFromSymbol(host_out, janus::gemm_dbg, sizeof(unsigned long long) * 8) == cudaSuccess ? 0 : -1;
+}
+#endif
 
 using namespace janus;
 
