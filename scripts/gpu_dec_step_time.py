@@ -7,6 +7,8 @@ from janus_b200.whisper.config import PRESETS
 from janus_b200.whisper.engine import WhisperEngine, DecodeSession
 from janus_b200.whisper.weights import init_random_weights
 B = int(os.environ.get("B", "1024"))
+if "PDL" in os.environ:
+    _abi.lib().janus_set_pdl(int(os.environ["PDL"]))
 dims = PRESETS["small"]
 eng = WhisperEngine(dims, init_random_weights(dims, seed=0, profile="confident"))
 ses = DecodeSession(eng, B, 128, steps_per_graph=10)
