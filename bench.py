@@ -335,6 +335,7 @@ def main() -> None:
     ap.add_argument("--lane-batch", type=int, default=1024, help="windows per decode lane (stt_prosody)")
     ap.add_argument("--lanes", type=int, default=0, help="decode lanes in flight (0 = 2 x batch / lane_batch)")
     ap.add_argument("--steps-per-graph", type=int, default=10)
+    ap.add_argument("--enc-chunk", type=int, default=64, help="encoder micro-batch (windows per encoder pass)")
     ap.add_argument("--fused", action="store_true", help="fused persistent segment kernel instead of per-op decode kernels")
     ap.add_argument("--max-new-tokens", type=int, default=128)
     ap.add_argument("--streams", type=int, default=4096, help="streams per GPU (prosody workload)")

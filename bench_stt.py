@@ -19,12 +19,14 @@ def stt_config(args, batch: int) -> dict:
                     "on the same windows -> MessagePack packets (BASELINE configs[2] + prosody)",
         "windows_per_gpu": batch, "lane_batch": min(args.lane_batch, batch), "clip_seconds": args.clip_seconds,
         "sample_rate": args.sample_rate, "max_new_tokens": args.max_new_tokens,
-        "pipeline": "per call: windows split into lanes of lane_batch; encoder stream (prosody, log-mel, encoder, "
-                    "cross-KV) runs lane by lane while earlier lanes decode on their own streams; calls are enqueued "
+        "pipeline": "per call: windows split into lanes of lane_batch; encoder stream (prosody, log-mel, encoder into "
+                    "the lane's encoder-state buffer) runs lane by lane while earlier lanes decode on their own streams "
+                    "(latent cross-attention over the encoder states for lanes >= 128 windows); calls are enqueued "
                     "back to back and fully drained inside the timed region",
         "parallelism": f"dp{args.gpus} over independent windows, no collective",
-        "encoder_micro_batch": 64,
-        "l2": "per-step working set (cross-KV 56 MB per window + activations) is far larger than the 126 MB L2",
+        "encoder_micro_batch": getattr(args, "enc_chunk", 64),
+        "l2": "per-step working set (encoder states 2.3 MB per window read once per layer and decode step, i.e. "
+              "2.4 GB per launch at 1024 windows, + activations) is far larger than the 126 MB L2",
     }
 
 
@@ -129,7 +131,7 @@ def run_gpu_stt(args) -> None:
     enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
                           prosody_sample_rate=sr, input_sample_rate=sr, lane_batch=args.lane_batch,
                           n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph,
-                          fused=args.fused)
+                          fused=args.fused, enc_chunk=getattr(args, "enc_chunk", 64))
     N = int(round(seconds * sr))
     x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)
     lengths = tuple([N] * B)
