@@ -204,7 +204,7 @@ typedef struct {
 #define JANUS_DECODE_FUSED 2
 /* JANUS_DECODE_LATENT: cross-attention reads the encoder states (state->enc_out) instead of per-layer K/V
  * caches -- half the HBM bytes per step, no cross_k / cross_v at all (janus_b200/csrc/dec_xlat.cu). Needs
- * d % 128 == 0, d <= 768, the w_ck_lat / w_cv / b_cv layer weights and state->enc_out / qlat / zlat. */
+ * d % 128 == 0, d <= 1024, <= 16 heads, the w_ck_lat / w_cv / b_cv layer weights and state->enc_out / qlat / zlat. */
 #define JANUS_DECODE_LATENT 4
 
 typedef struct {
@@ -245,7 +245,8 @@ int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k, const void
 /* Decode-time cross-attention over the encoder states themselves ("latent" form, K/V projections absorbed
  * into the query and output sides -- janus_b200/csrc/dec_xlat.cu): qlat bf16 [n_windows, 16, d] (absorbed
  * queries Wk_h^T q_h, rows >= n_heads zero), enc bf16 [n_windows, n_ctx, d]; z bf16 [n_windows, n_heads, d]
- * = softmax_t(enc . qlat_h / 8) @ enc. Needs d % 128 == 0, d <= 768, d == 64 * n_heads. */
+ * = softmax_t(enc . qlat_h / 8) @ enc. Needs d % 128 == 0, d <= 1024, d == 64 * n_heads, n_heads <= 16
+ * (d <= 768: one-tile ring kernel; d = 1024: streaming two-pass kernel). */
 int32_t janus_dec_xlat_bf16(const void* qlat, const void* enc, void* z, int32_t n_windows, int32_t n_ctx, int32_t d,
                             int32_t n_heads, void* stream);
 /* Cross-attention K/V of all decoder layers for a batch of encoder outputs (one tcgen05 GEMM whose

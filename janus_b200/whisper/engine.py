@@ -135,8 +135,10 @@ def _pack_decoder(self, W) -> None:
     n, L = d.n_text_state, d.n_text_layer
     self.c_dec_dims = DimsStruct(d.n_mels, d.n_audio_ctx, n, d.n_text_head, L)
     self.dec_layers = (DecLayerStruct * L)()
-    # latent cross-attention (dec_xlat.cu) holds one 128-key tile of encoder states in shared memory: d <= 768
-    self.latent_ok = n % 128 == 0 and n <= 768 and n == 64 * d.n_text_head and d.n_audio_state == n
+    # latent cross-attention (dec_xlat.cu): d <= 768 holds one 128-key tile of encoder states in shared memory,
+    # d = 1024 (medium) streams every tile twice (second pass from L2); 16 heads at most (MMA N = 16)
+    self.latent_ok = n % 128 == 0 and n <= 1024 and d.n_text_head <= 16 and n == 64 * d.n_text_head and \
+        d.n_audio_state == n
     ckv_w, ckv_b = [], []
     for i in range(L):
         p = f"dec.l{i}"
@@ -221,7 +223,7 @@ class DecodeSession:
         if latent is None:
             latent = engine.latent_ok and not light and not fused and B >= self.LATENT_MIN_BATCH
         if latent and not engine.latent_ok:
-            raise ValueError("latent cross-attention needs d % 128 == 0 and d <= 768")
+            raise ValueError("latent cross-attention needs d % 128 == 0, d <= 1024 and <= 16 heads")
         if latent and (light or fused):
             raise ValueError("latent cross-attention excludes light / fused decode sessions")
         self.latent = latent
