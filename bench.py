@@ -338,6 +338,9 @@ def main() -> None:
     ap.add_argument("--enc-chunk", type=int, default=64, help="encoder micro-batch (windows per encoder pass)")
     ap.add_argument("--fused", action="store_true", help="fused persistent segment kernel instead of per-op decode kernels")
     ap.add_argument("--max-new-tokens", type=int, default=128)
+    ap.add_argument("--beam", type=int, default=0,
+                    help="0 = greedy (the reference's call: beam_size=1); K >= 1 = beam search with K beams per window "
+                         "(BASELINE configs[3] uses 5)")
     ap.add_argument("--streams", type=int, default=4096, help="streams per GPU (prosody workload)")
     ap.add_argument("--clip-seconds", type=float, default=30.0)
     ap.add_argument("--sample-rate", type=int, default=16000)

@@ -13,11 +13,13 @@ from bench import METRIC, ROOT, UNIT, ClockSampler, cpu_prosody_throughput
 
 
 def stt_config(args, batch: int) -> dict:
+    beam = getattr(args, "beam", 0)
+    decode = f"beam-{beam} search decode" if beam else "greedy decode"
     return {
-        "workload": f"Whisper-{args.model} (random-init, bf16) log-mel + encoder + greedy decode of "
+        "workload": f"Whisper-{args.model} (random-init, bf16) log-mel + encoder + {decode} of "
                     f"{args.max_new_tokens} tokens per 30 s window, plus aubio-equivalent YIN pitch / RMS prosody "
                     "on the same windows -> MessagePack packets (BASELINE configs[2] + prosody)",
-        "windows_per_gpu": batch, "lane_batch": min(args.lane_batch, batch), "clip_seconds": args.clip_seconds,
+        "beam": beam, "windows_per_gpu": batch, "lane_batch": min(args.lane_batch, batch), "clip_seconds": args.clip_seconds,
         "sample_rate": args.sample_rate, "max_new_tokens": args.max_new_tokens,
         "pipeline": "per call: windows split into lanes of lane_batch; encoder stream (prosody, log-mel, encoder into "
                     "the lane's encoder-state buffer) runs lane by lane while earlier lanes decode on their own streams "
@@ -56,7 +58,10 @@ def cpu_stt_prosody(args, n_windows: int, cores: int):
         enc = R.encode(W, dims, mel)
         t_enc = time.perf_counter() - t0
         t0 = time.perf_counter()
-        toks, _ = R.greedy_decode(W, dims, spec, enc, args.max_new_tokens, stop_at_eot=False)
+        if getattr(args, "beam", 0):
+            toks, _ = R.beam_decode(W, dims, spec, enc, args.max_new_tokens, beam_size=args.beam)
+        else:
+            toks, _ = R.greedy_decode(W, dims, spec, enc, args.max_new_tokens, stop_at_eot=False)
         t_dec = time.perf_counter() - t0
     pros_rate, t_pros, lph = cpu_prosody_throughput(n_windows, args.clip_seconds, args.sample_rate, min(cores, n_windows))
     t0 = time.perf_counter()
@@ -131,7 +136,8 @@ def run_gpu_stt(args) -> None:
     enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
                           prosody_sample_rate=sr, input_sample_rate=sr, lane_batch=args.lane_batch,
                           n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph,
-                          fused=args.fused, enc_chunk=getattr(args, "enc_chunk", 64))
+                          fused=args.fused, enc_chunk=getattr(args, "enc_chunk", 64), beam=getattr(args, "beam", 0))
+    beam = max(getattr(args, "beam", 0), 1)
     N = int(round(seconds * sr))
     x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)
     lengths = tuple([N] * B)
@@ -219,7 +225,11 @@ def run_gpu_stt(args) -> None:
         for ln in enc.lanes[:enc.lanes_per_call]:
             s_ = ln.session
             for l in range(d.n_text_layer):
-                if latent:
+                if latent and beam > 1:   # the beams of a window share its encoder states
+                    _abi.call("janus_dec_xlat_grouped_bf16", s_.qlat.data_ptr(), s_.enc_buf.data_ptr(),
+                              s_.zlat.data_ptr(), lb * beam, beam, d.n_audio_ctx, d.n_text_state, d.n_text_head,
+                              stream.cuda_stream)
+                elif latent:
                     _abi.call("janus_dec_xlat_bf16", s_.qlat.data_ptr(), s_.enc_buf.data_ptr(), s_.zlat.data_ptr(), lb,
                               d.n_audio_ctx, d.n_text_state, d.n_text_head, stream.cuda_stream)
                 else:
@@ -287,7 +297,7 @@ def run_gpu_stt(args) -> None:
         H, T, kv_ld = d.n_text_head, d.n_audio_ctx, enc.whisper.kv_ld
         # algorithmic bytes of one cross-attention launch: K and V of every (stream, head) once, q in, out out
         if latent:   # the encoder states of every window once, absorbed queries (16 rows) in, z out
-            alg_bytes = lb * T * d.n_text_state * 2 + lb * (16 + H) * d.n_text_state * 2
+            alg_bytes = lb * T * d.n_text_state * 2 + lb * beam * (16 + H) * d.n_text_state * 2
         else:
             alg_bytes = lb * H * (2 * T * 64 * 2) + 2 * lb * d.n_text_state * 2
         achieved = alg_bytes / (xattn_ms / 1e3) / 1e9
@@ -299,7 +309,7 @@ def run_gpu_stt(args) -> None:
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "r01_xlat_traffic.json" if latent else
                                              "r01_xattn_traffic.json")))
-            if (tj["lane_batch"], tj["n_heads"], tj["n_ctx"]) == (lb, H, T):
+            if (tj["lane_batch"], tj["n_heads"], tj["n_ctx"]) == (lb, H, T) and beam == 1:
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
         except Exception:  # noqa: BLE001
             pass

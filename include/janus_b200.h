@@ -259,6 +259,50 @@ int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* dims, const janu
 int32_t janus_whisper_decode_step(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,
                                   const janus_decode_state_t* state, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * K3, beam search (BASELINE configs[3]: beam 5). Replaces what CTranslate2 `Whisper.generate(beam_size=5,
+ * patience=1, length_penalty=1)` does when faster-whisper's `transcribe(beam_size=5)` is called; the reference's
+ * own call site passes beam_size=1 (backend/services/transcriber.py:55), which is janus_whisper_decode_step.
+ * Algorithm = the published OpenAI Whisper BeamSearchDecoder / MaximumLikelihoodRanker (oracle/whisper_ref.py
+ * beam_decode states it step by step).
+ *
+ * Rows of the decode state are the beams of n_streams streams: state->batch == n_streams * beam, row = stream * beam
+ * + k; state->tokens is [rows, max_len] with the prompt pre-filled in every row. Cross-attention inputs exist once
+ * per STREAM (state->enc_out [n_streams, n_ctx, d] or cross_k / cross_v with batch = n_streams); the self-attention
+ * caches hold one slot per row and are never copied on a beam reorder: indir[row][j] names the slot (0 .. beam-1
+ * within the stream) that holds position j of row's hypothesis. state->forced / choice / logprob / sum_logprob /
+ * done are not used.
+ * ------------------------------------------------------------------------------------------ */
+#define JANUS_MAX_BEAM 8
+typedef struct {
+  int32_t beam, n_streams;
+  int32_t max_candidates;              /* round(beam * patience): finished hypotheses kept per stream */
+  int32_t reserved0;
+  float* cum;                          /* [rows] cumulative log-prob of the live beams; reset to 0, -inf, -inf, ... per stream */
+  uint8_t* indir;                      /* [rows, self_ld]; reset to indir[row][j] = row % beam */
+  float* cand_score;                   /* [rows, beam + 1] scratch: candidates of the current step */
+  int32_t* cand_tok;                   /* [rows, beam + 1] */
+  int32_t* fin_tokens;                 /* [n_streams, max_candidates, max_len] finished hypotheses (prompt .. eot) */
+  float* fin_score;                    /* [n_streams, max_candidates] their sum of log-probs (eot included) */
+  int32_t* fin_len;                    /* [n_streams, max_candidates] sampled tokens before eot */
+  int32_t* n_fin;                      /* [n_streams]; reset to 0 */
+  uint8_t* stream_done;                /* [n_streams]; 1 once n_fin == max_candidates (state->n_done counts them) */
+} janus_beam_state_t;
+
+/* One beam-search step for every stream: consumes tokens[:, *pos] of every row, chooses the next beams, rewrites the
+ * rows' token histories and the indirection in place, then *pos += 1. Graph-capturable like the greedy step. */
+int32_t janus_whisper_decode_beam_step(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,
+                                       const janus_decode_state_t* state, const janus_beam_state_t* beam, void* stream);
+/* After the last step: per stream, the pool = finished hypotheses (+ live beams by descending score while it holds
+ * fewer than `beam`); best = argmax score / n_tokens. best_tokens int32 [n_streams, max_len] (prompt, sampled tokens,
+ * eot padding), best_score [n_streams] sum of log-probs, best_len [n_streams] sampled tokens before eot. */
+int32_t janus_whisper_beam_finalize(const janus_decode_state_t* state, const janus_beam_state_t* beam, int32_t eot,
+                                    int32_t* best_tokens, float* best_score, int32_t* best_len, void* stream);
+/* janus_dec_xlat_bf16 for rows that share encoder states in groups (beam search): qlat [n_rows, 16, d],
+ * enc [n_rows / group, n_ctx, d], z [n_rows, n_heads, d]. */
+int32_t janus_dec_xlat_grouped_bf16(const void* qlat, const void* enc, void* z, int32_t n_rows, int32_t group,
+                                    int32_t n_ctx, int32_t d, int32_t n_heads, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

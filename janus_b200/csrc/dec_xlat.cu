@@ -216,7 +216,7 @@ __device__ __forceinline__ void xl_softmax_warps(int warp, int lane, uint32_t tm
 
 __global__ void __launch_bounds__(XL_THREADS, 1)
 dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_q,
-                __nv_bfloat16* z, int T, int d, int n_heads, int n_windows, float scale_log2) {
+                __nv_bfloat16* z, int T, int d, int n_heads, int n_windows, float scale_log2, int x_group) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int nb = d >> 6;     // 64-feature boxes per tile
@@ -282,7 +282,7 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           if (g > 0) mbar_wait(&box_empty[kb], (g - 1) & 1);
           if (leader) {
             mbar_arrive_expect_tx(&box_full[kb], XL_BOX_BYTES);
-            tma_load_3d(sX + kb * XL_BOX_BYTES, &tmap_x, &box_full[kb], kb * 64, t * XL_KEYS, w);
+            tma_load_3d(sX + kb * XL_BOX_BYTES, &tmap_x, &box_full[kb], kb * 64, t * XL_KEYS, w / x_group);
           }
           __syncwarp();
         }
@@ -292,7 +292,7 @@ dec_xlat_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constan
           int tn = t + 1, wn = w;
           if (tn == n_tiles) { tn = 0; wn = w + gridDim.x; }
           if (wn < n_windows) {
-            for (int kb = 0; kb < nb; ++kb) tma_prefetch_3d(&tmap_x, kb * 64, tn * XL_KEYS, wn);
+            for (int kb = 0; kb < nb; ++kb) tma_prefetch_3d(&tmap_x, kb * 64, tn * XL_KEYS, wn / x_group);
             if (tn == 0)
               for (int kb = 0; kb < nb; ++kb) tma_prefetch_3d(&tmap_q, kb * 64, 0, wn);
           }
@@ -399,7 +399,8 @@ static size_t xlat2_smem_bytes(int d) {
 
 __global__ void __launch_bounds__(XL_THREADS, 1)
 dec_xlat2_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_q,
-                 __nv_bfloat16* z, int T, int d, int n_heads, int n_windows, float scale_log2, int PS, int tmem_cols) {
+                 __nv_bfloat16* z, int T, int d, int n_heads, int n_windows, float scale_log2, int PS, int tmem_cols,
+                 int x_group) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   const int nb = d >> 6;     // 64-feature boxes per tile
@@ -476,8 +477,8 @@ dec_xlat2_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
           if (leader) {
             uint8_t* dst = sX + slot * XL_PAIR_BYTES;
             mbar_arrive_expect_tx(&full[slot], XL_PAIR_BYTES);
-            tma_load_3d(dst, &tmap_x, &full[slot], (2 * fb) * 64, t * XL_KEYS, w);
-            tma_load_3d(dst + XL_BOX_BYTES, &tmap_x, &full[slot], (2 * fb + 1) * 64, t * XL_KEYS, w);
+            tma_load_3d(dst, &tmap_x, &full[slot], (2 * fb) * 64, t * XL_KEYS, w / x_group);
+            tma_load_3d(dst + XL_BOX_BYTES, &tmap_x, &full[slot], (2 * fb + 1) * 64, t * XL_KEYS, w / x_group);
           }
           __syncwarp();
         }
@@ -557,14 +558,18 @@ dec_xlat2_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   }
 }
 
-// qlat [n_windows, 16, d] (rows >= n_heads zero), enc [n_windows, T, d], z [n_windows, n_heads, d]
+// qlat [n_windows, 16, d] (rows >= n_heads zero), enc [n_windows / x_group, T, d], z [n_windows, n_heads, d].
+// x_group > 1 (beam search): x_group consecutive query rows attend to the same encoder states; they are walked by
+// neighbouring CTAs at the same time, so that one of them pulls a tile from HBM and the others hit it in L2.
 int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16* z, int n_windows, int T, int d,
-             int n_heads, cudaStream_t stream) {
+             int n_heads, cudaStream_t stream, int x_group) {
+  JANUS_CHECK_ARG(x_group >= 1 && n_windows % x_group == 0, "xlat: n_windows=%d is not a multiple of x_group=%d",
+                  n_windows, x_group);
   JANUS_CHECK_ARG(d % 128 == 0 && d <= 1024 && n_heads <= XL_HP && n_heads * 64 == d,
                   "xlat: d=%d / n_heads=%d unsupported (need d %% 128 == 0, d <= 1024, <= 16 heads)", d, n_heads);
   CUtensorMap tx, tq;
   {
-    const uint64_t dims[3] = {(uint64_t)d, (uint64_t)T, (uint64_t)n_windows};
+    const uint64_t dims[3] = {(uint64_t)d, (uint64_t)T, (uint64_t)(n_windows / x_group)};
     const uint64_t str[2] = {(uint64_t)d * 2, (uint64_t)T * d * 2};
     const uint32_t box[3] = {64, XL_KEYS, 1};
     int rc = make_tmap_bf16(&tx, enc, 3, dims, str, box);
@@ -602,7 +607,7 @@ int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16*
       attr2 = smem;
     }
     JANUS_CUDA(launch_pdl(dec_xlat2_kernel, dim3(grid), dim3(XL_THREADS), smem, stream, tx, tq, z, T, d, n_heads,
-                          n_windows, scale_log2, ps, tmem_cols));
+                          n_windows, scale_log2, ps, tmem_cols, x_group));
     return JANUS_OK;
   }
   const size_t smem = xlat_smem_bytes(d);
@@ -612,7 +617,7 @@ int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16*
     attr_bytes = smem;
   }
   JANUS_CUDA(launch_pdl(dec_xlat_kernel, dim3(grid), dim3(XL_THREADS), smem, stream, tx, tq, z, T, d, n_heads,
-                        n_windows, scale_log2));
+                        n_windows, scale_log2, x_group));
   return JANUS_OK;
 }
 
@@ -628,5 +633,11 @@ extern "C" int32_t janus_dec_xlat_bf16(const void* qlat, const void* enc, void* 
                                        int32_t d, int32_t n_heads, void* stream) {
   JANUS_CHECK_ARG(qlat && enc && z && n_windows > 0 && n_ctx > 0, "xlat: bad argument");
   return janus::dec_xlat(static_cast<const __nv_bfloat16*>(qlat), static_cast<const __nv_bfloat16*>(enc),
-                         static_cast<__nv_bfloat16*>(z), n_windows, n_ctx, d, n_heads, (cudaStream_t)stream);
+                         static_cast<__nv_bfloat16*>(z), n_windows, n_ctx, d, n_heads, (cudaStream_t)stream, 1);
+}
+extern "C" int32_t janus_dec_xlat_grouped_bf16(const void* qlat, const void* enc, void* z, int32_t n_rows, int32_t group,
+                                               int32_t n_ctx, int32_t d, int32_t n_heads, void* stream) {
+  JANUS_CHECK_ARG(qlat && enc && z && n_rows > 0 && n_ctx > 0 && group > 0, "xlat: bad argument");
+  return janus::dec_xlat(static_cast<const __nv_bfloat16*>(qlat), static_cast<const __nv_bfloat16*>(enc),
+                         static_cast<__nv_bfloat16*>(z), n_rows, n_ctx, d, n_heads, (cudaStream_t)stream, group);
 }

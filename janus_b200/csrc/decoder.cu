@@ -53,9 +53,13 @@ __global__ void dec_embed_kernel(const int32_t* tokens, int max_len, const int32
 constexpr int SA_WARPS = 4;
 constexpr int SA_MAXCTX = 512;
 
+// BEAM: the rows of a stream's beams (row = stream * beam + k) keep appending to their own cache slot; which slot
+// holds position j of row's hypothesis is looked up in indir[row][j] (beam index within the stream), so a beam
+// reorder rewrites `beam * n_ctx` bytes of indices per stream instead of copying K/V rows (dec_beam.cu).
+template <bool BEAM>
 __global__ void __launch_bounds__(SA_WARPS * 32)
 dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos_p, int d,
-                     int n_ctx, int H, int n_items, __nv_bfloat16* out) {
+                     int n_ctx, int H, int n_items, __nv_bfloat16* out, const uint8_t* indir, int beam) {
   __shared__ float ps_all[SA_WARPS][SA_MAXCTX];
   __shared__ float qs_all[SA_WARPS][DH];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -87,10 +91,18 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
 #pragma unroll
   for (int i = 0; i < 8; ++i) qf[i] = qs[c8 * 8 + i];
   const uint4* kp = reinterpret_cast<const uint4*>(K) + c8;
+  // BEAM: uint4 offset of slot s relative to this row's own cache
+  const long long slot_stride = (long long)H * n_ctx * 8;
+  const uint8_t* ind = BEAM ? indir + (long long)b * n_ctx : nullptr;
+  const int self_slot = BEAM ? b % beam : 0;
 #pragma unroll 4
   for (int j0 = 0; j0 <= pos; j0 += 4) {   // warp-uniform trip count (the shuffles below need every lane)
     const int j = j0 + jg;
-    const uint4 u = j <= pos ? kp[(long long)j * 8] : make_uint4(0, 0, 0, 0);
+    uint4 u = make_uint4(0, 0, 0, 0);
+    if (j <= pos) {
+      if (BEAM) u = kp[(long long)j * 8 + ((int)ind[j] - self_slot) * slot_stride];
+      else u = kp[(long long)j * 8];
+    }
     const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
     float s = 0.f;
 #pragma unroll
@@ -123,7 +135,7 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
   const uint4* vp = reinterpret_cast<const uint4*>(V) + c8;
 #pragma unroll 4
   for (int j = jg; j <= pos; j += 4) {
-    const uint4 u = vp[(long long)j * 8];
+    const uint4 u = BEAM ? vp[(long long)j * 8 + ((int)ind[j] - self_slot) * slot_stride] : vp[(long long)j * 8];
     const float p = ps[j];
     const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
@@ -156,7 +168,7 @@ constexpr int XA_THREADS = 192;  // 192 * 8 keys = 1536 >= 1500
 __global__ void __launch_bounds__(XA_THREADS)
 dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kT,
                       const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, int H, int n_items,
-                      __nv_bfloat16* out) {
+                      __nv_bfloat16* out, int kv_group) {
   // 6.4 KB of shared memory and 40 registers per thread: with the grid capped at 3 CTAs per SM (xa_grid)
   // three of these fit beside one persistent tcgen05 GEMM CTA of the encoder stream (198 KB, 41 K registers)
   __shared__ float qs[DH];
@@ -168,7 +180,7 @@ dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ 
   pdl_wait();
   for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
   const int b = item / H, h = item - b * H;
-  const long long bh = (long long)b * H + h;
+  const long long bh = (long long)(b / kv_group) * H + h;   // kv_group beams of a stream share its K/V (L2 hits)
   if (tid < DH) qs[tid] = __bfloat162float(q[(long long)b * d + h * DH + tid]) * (0.125f * 1.4426950408889634f);
   __syncthreads();
   // ---- scores for keys 8*tid .. 8*tid+7
@@ -445,7 +457,7 @@ extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k,
   dec_cross_attn_kernel<<<xa_grid(n_heads * batch), XA_THREADS, 0, (cudaStream_t)stream>>>(
       static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(cross_k),
       static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, n_heads, n_heads * batch,
-      static_cast<__nv_bfloat16*>(out));
+      static_cast<__nv_bfloat16*>(out), 1);
   JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
   return JANUS_OK;
 }
@@ -465,9 +477,16 @@ extern "C" int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* c, co
                    static_cast<const __nv_bfloat16*>(w->w_ckv), d, p, (cudaStream_t)stream);
 }
 
-extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
-                                             const janus_decode_state_t* s, void* stream_) {
+// One decode step for s->batch rows. bm == nullptr: greedy (a row is a stream). bm != nullptr: beam search, rows are
+// the beams of bm->n_streams streams (row = stream * beam + k): self-attention follows the beam indirection, the
+// cross-attention of a stream's beams reads the same encoder states / K/V, and the token choice is the candidate /
+// update pair of dec_beam.cu.
+static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                const janus_decode_state_t* s, const janus_beam_state_t* bm, void* stream_) {
   JANUS_CHECK_ARG(c && w && s, "decode_step: null pointer");
+  const int grp = bm ? bm->beam : 1;
+  JANUS_CHECK_ARG(!bm || !(s->flags & (JANUS_DECODE_LIGHT | JANUS_DECODE_FUSED)),
+                  "decode_beam_step: LIGHT / FUSED sessions are greedy only");
   JANUS_CHECK_ARG(c->d == c->n_heads * 64, "decode_step: head_dim must be 64");
   JANUS_CHECK_ARG(c->n_ctx <= XA_THREADS * 8 && w->kv_ld % 8 == 0 && w->kv_ld >= c->n_ctx && w->kv_ld <= XA_THREADS * 8,
                   "decode_step: n_ctx=%d / kv_ld=%d unsupported", c->n_ctx, w->kv_ld);
@@ -495,8 +514,8 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   JANUS_CHECK_ARG(self_ld >= s->max_len && self_ld <= 512, "decode_step: self_ld=%d must be in [max_len=%d, 512]", self_ld,
                   s->max_len);
   const long long self_stride = (long long)B * H * self_ld * DH;
-  const long long ck_stride = (long long)B * H * DH * w->kv_ld;
-  const long long cv_stride = (long long)B * H * T * DH;
+  const long long ck_stride = (long long)(B / grp) * H * DH * w->kv_ld;   // cross K/V exist once per stream
+  const long long cv_stride = (long long)(B / grp) * H * T * DH;
   if (fused) {
     FusedProgram base = {};
     base.rows = B; base.d = d; base.n_heads = H; base.pos = s->pos;
@@ -534,7 +553,7 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
       if ((rc = dec_fused_segment(P, st))) return rc;
       JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                             static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
+                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att, 1));
     }
     FusedProgram P = base;
     tail_of(P, w->layers[c->n_layers - 1]);
@@ -550,9 +569,17 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
     const janus_dec_layer_t& L = w->layers[l];
     if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st, light))) return rc;
-    JANUS_CUDA(launch_pdl(dec_self_attn_kernel, dim3((H * B + SA_WARPS - 1) / SA_WARPS), dim3(SA_WARPS * 32), 0, st, qkv,
+    if (bm) {
+      JANUS_CUDA(launch_pdl(dec_self_attn_kernel<true>, dim3((H * B + SA_WARPS - 1) / SA_WARPS), dim3(SA_WARPS * 32), 0, st,
+                            qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
+                            static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, H, H * B, att,
+                            bm->indir, bm->beam));
+    } else {
+    JANUS_CUDA(launch_pdl(dec_self_attn_kernel<false>, dim3((H * B + SA_WARPS - 1) / SA_WARPS), dim3(SA_WARPS * 32), 0, st, qkv,
                           static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
-                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, H, H * B, att));
+                          static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, H, H * B, att,
+                          static_cast<const uint8_t*>(nullptr), 1));
+    }
     if ((rc = linear(att, d, L.w_o, L.b_o, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.lnc_w, L.lnc_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_cq, L.b_cq, nullptr, q, B, d, ACT_NONE, 0, st, light))) return rc;
@@ -567,7 +594,7 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
         g.store_mode = STORE_ROWMAJOR; g.w_batch_rows = d;
         if ((rc = gemm_bf16(q, d, DH, static_cast<const __nv_bfloat16*>(L.w_ck_lat), DH, g, st))) return rc;
       }
-      if ((rc = dec_xlat(qlat, static_cast<const __nv_bfloat16*>(s->enc_out), zlat, B, T, d, H, st))) return rc;
+      if ((rc = dec_xlat(qlat, static_cast<const __nv_bfloat16*>(s->enc_out), zlat, B, T, d, H, st, grp))) return rc;
       {   // att[b, h*64 .. h*64+63] = zlat[b, h, :] . Wv_h^T + bv_h   (grouped over heads, N = 64)
         GemmParams g = {};
         g.M_per_batch = B; g.n_batch = H; g.N = DH; g.K = d;
@@ -579,7 +606,7 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
     } else {
     JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                           static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
+                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att, grp));
     }
     if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
@@ -589,6 +616,16 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
   }
   if ((rc = linear(xn, d, w->tok_emb, nullptr, nullptr, s->logits, B, w->n_vocab_pad, ACT_NONE, 1, st, light))) return rc;
+  if (bm) {
+    BeamStepParams bp = {};
+    bp.logits = s->logits; bp.suppress = w->suppress_mask; bp.tokens = s->tokens; bp.pos = s->pos; bp.n_done = s->n_done;
+    bp.n_vocab = w->n_vocab; bp.n_vocab_pad = w->n_vocab_pad; bp.max_len = s->max_len; bp.n_prompt = s->n_prompt;
+    bp.eot = w->eot; bp.blank = w->blank; bp.ts_begin = w->timestamp_begin; bp.max_initial_ts = w->max_initial_timestamp_index;
+    bp.self_ld = self_ld; bp.bm = *bm;
+    if ((rc = dec_beam_step(bp, st))) return rc;
+    JANUS_CUDA(launch_pdl(dec_advance_kernel, dim3(1), dim3(1), 0, st, s->pos));
+    return JANUS_OK;
+  }
   PickParams pp;
   pp.logits = s->logits; pp.suppress = w->suppress_mask; pp.tokens = s->tokens; pp.forced = s->forced;
   pp.choice = s->choice; pp.logprob = s->logprob; pp.sum_logprob = s->sum_logprob; pp.pos = s->pos;
@@ -598,4 +635,30 @@ extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, cons
   JANUS_CUDA(launch_pdl(dec_pick_kernel, dim3(B), dim3(PICK_THREADS), 0, st, pp));
   JANUS_CUDA(launch_pdl(dec_advance_kernel, dim3(1), dim3(1), 0, st, s->pos));
   return JANUS_OK;
+}
+
+extern "C" int32_t janus_whisper_decode_step(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                             const janus_decode_state_t* s, void* stream) {
+  return decode_step_impl(c, w, s, nullptr, stream);
+}
+
+extern "C" int32_t janus_whisper_decode_beam_step(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                                  const janus_decode_state_t* s, const janus_beam_state_t* bm,
+                                                  void* stream) {
+  JANUS_CHECK_ARG(bm && s, "decode_beam_step: null pointer");
+  JANUS_CHECK_ARG(bm->beam >= 1 && bm->beam <= JANUS_MAX_BEAM && bm->n_streams > 0 && s->batch == bm->n_streams * bm->beam,
+                  "decode_beam_step: batch=%d must be n_streams=%d x beam=%d (beam <= %d)", s->batch, bm->n_streams,
+                  bm->beam, JANUS_MAX_BEAM);
+  JANUS_CHECK_ARG(bm->max_candidates >= 1 && bm->max_candidates <= 2 * JANUS_MAX_BEAM, "decode_beam_step: max_candidates=%d",
+                  bm->max_candidates);
+  JANUS_CHECK_ARG(bm->cum && bm->indir && bm->cand_score && bm->cand_tok && bm->fin_tokens && bm->fin_score && bm->fin_len &&
+                  bm->n_fin && bm->stream_done, "decode_beam_step: beam state has null buffers");
+  return decode_step_impl(c, w, s, bm, stream);
+}
+
+extern "C" int32_t janus_whisper_beam_finalize(const janus_decode_state_t* s, const janus_beam_state_t* bm, int32_t eot,
+                                               int32_t* best_tokens, float* best_score, int32_t* best_len, void* stream) {
+  JANUS_CHECK_ARG(s && bm && best_tokens && best_score && best_len, "beam_finalize: null pointer");
+  return dec_beam_finalize(s->tokens, s->pos, s->max_len, s->n_prompt, eot, *bm, best_tokens, best_score, best_len,
+                           (cudaStream_t)stream);
 }

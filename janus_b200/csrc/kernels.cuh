@@ -36,11 +36,29 @@ int layernorm_bf16(const __nv_bfloat16* x, const float* w, const float* b, __nv_
 int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int T, int n_heads, cudaStream_t stream);
 int num_sms();
 // latent cross-attention (dec_xlat.cu): qlat [n, 16, d] absorbed queries, enc [n, T, d] encoder states -> z [n, H, d]
+// (x_group > 1: x_group consecutive query rows share one window of encoder states -- beam search)
 int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16* z, int n_windows, int T, int d,
-             int n_heads, cudaStream_t stream);
+             int n_heads, cudaStream_t stream, int x_group = 1);
 int dec_linear(const __nv_bfloat16* A, int lda, const __nv_bfloat16* W, const float* bias,
                const __nv_bfloat16* residual, void* out, int rows, int N, int K, int act, int out_f32,
                cudaStream_t stream, bool pdl = false);
+
+// ---- beam search bookkeeping (dec_beam.cu) ------------------------------------------------------
+struct BeamStepParams {
+  const float* logits;        // [rows, n_vocab_pad]
+  const uint8_t* suppress;
+  int32_t* tokens;            // [rows, max_len]
+  int32_t* pos;
+  int32_t* n_done;
+  int n_vocab, n_vocab_pad, max_len, n_prompt, eot, blank, ts_begin, max_initial_ts, self_ld;
+  janus_beam_state_t bm;
+};
+// candidates (rule filter + log-softmax + top beam+1 per row), then per stream: selection, finished list, in-place
+// reorder of token histories / indirection
+int dec_beam_step(const BeamStepParams& p, cudaStream_t stream);
+int dec_beam_finalize(const int32_t* tokens, const int32_t* pos, int max_len, int n_prompt, int eot,
+                      const janus_beam_state_t& bm, int32_t* best_tokens, float* best_score, int32_t* best_len,
+                      cudaStream_t stream);
 
 // ---- fused decode segment (dec_fused.cu) -------------------------------------------------------
 enum FusedPhaseType { FZ_LINEAR = 0, FZ_SELF_ATTN = 1, FZ_LAYERNORM = 2 };

@@ -130,6 +130,12 @@ class DecodeStateStruct(C.Structure):
                                           "att", "q", "ff", "logits", "barrier", "enc_out", "qlat", "zlat")]
 
 
+class BeamStateStruct(C.Structure):
+    _fields_ = [("beam", C.c_int32), ("n_streams", C.c_int32), ("max_candidates", C.c_int32), ("reserved0", C.c_int32)] + \
+               [(n, C.c_void_p) for n in ("cum", "indir", "cand_score", "cand_tok", "fin_tokens", "fin_score", "fin_len",
+                                          "n_fin", "stream_done")]
+
+
 def _pack_decoder(self, W) -> None:
     d, spec = self.dims, self.spec
     n, L = d.n_text_state, d.n_text_layer
@@ -187,7 +193,9 @@ WhisperEngine._pack_decoder = _pack_decoder
 
 
 class DecodeSession:
-    """Greedy decode of a fixed-size batch: owns the KV caches and the captured CUDA graph of one step."""
+    """Greedy (beam = 0) or beam-search (beam >= 1) decode of a fixed-size batch of windows: owns the KV caches and
+    the captured CUDA graph of one step. With beam search the decode rows are the beams of the windows
+    (row = window * beam + k); cross-attention inputs exist once per window."""
 
     DECODE_LIGHT = 1   # JANUS_DECODE_LIGHT
     DECODE_FUSED = 2   # JANUS_DECODE_FUSED
@@ -197,10 +205,17 @@ class DecodeSession:
 
     def __init__(self, engine: WhisperEngine, batch: int, max_new_tokens: int, use_graph: bool = True,
                  light: bool = False, steps_per_graph: int = 1, fused: bool = False,
-                 latent: bool | None = None) -> None:
+                 latent: bool | None = None, beam: int = 0, patience: float = 1.0) -> None:
         if not hasattr(engine, "dec_weights"):
             raise RuntimeError("engine was built without decoder weights")
+        if beam and (light or fused):
+            raise ValueError("beam search excludes light / fused decode sessions")
+        if not 0 <= beam <= 8:
+            raise ValueError("beam must be in 0 .. 8 (JANUS_MAX_BEAM)")
         self.eng, self.B = engine, batch
+        self.beam, self.n_windows = beam, batch
+        NW = batch                 # windows: cross-attention inputs, results
+        batch = batch * max(beam, 1)   # decode rows
         d, spec, dev = engine.dims, engine.spec, engine.device
         self.n_prompt = len(spec.sot_sequence)
         self.max_new = min(max_new_tokens, spec.max_length - self.n_prompt)
@@ -221,7 +236,7 @@ class DecodeSession:
         self.self_k = torch.zeros((L, B, H, self.self_ld, 64), **bf)
         self.self_v = torch.zeros((L, B, H, self.self_ld, 64), **bf)
         if latent is None:
-            latent = engine.latent_ok and not light and not fused and B >= self.LATENT_MIN_BATCH
+            latent = engine.latent_ok and not light and not fused and NW >= self.LATENT_MIN_BATCH
         if latent and not engine.latent_ok:
             raise ValueError("latent cross-attention needs d % 128 == 0, d <= 1024 and <= 16 heads")
         if latent and (light or fused):
@@ -230,12 +245,12 @@ class DecodeSession:
         if latent:
             # cross-attention over the encoder states themselves: no per-layer K/V (2 * L times smaller)
             self.cross_k = self.cross_v = None
-            self.enc_buf = torch.zeros((B, d.n_audio_ctx, n), **bf)
+            self.enc_buf = torch.zeros((NW, d.n_audio_ctx, n), **bf)
             self.qlat = torch.zeros((B, 16, n), **bf)      # rows >= H stay zero
             self.zlat = torch.zeros((B, H, n), **bf)
         else:
-            self.cross_k = torch.zeros((L, B, H, 64, engine.kv_ld), **bf)
-            self.cross_v = torch.zeros((L, B, H, d.n_audio_ctx, 64), **bf)
+            self.cross_k = torch.zeros((L, NW, H, 64, engine.kv_ld), **bf)
+            self.cross_v = torch.zeros((L, NW, H, d.n_audio_ctx, 64), **bf)
         self.x, self.xn = torch.zeros((B, n), **bf), torch.zeros((B, n), **bf)
         self.qkv, self.att = torch.zeros((B, 3 * n), **bf), torch.zeros((B, n), **bf)
         self.q, self.ff = torch.zeros((B, n), **bf), torch.zeros((B, 4 * n), **bf)
@@ -259,6 +274,35 @@ class DecodeSession:
         else:
             s.cross_k, s.cross_v = self.cross_k.data_ptr(), self.cross_v.data_ptr()
         self.state = s
+        self.beam_state = None
+        if beam:
+            K, MC = beam, max(1, int(round(beam * patience)))
+            if MC > 16:
+                raise ValueError("beam * patience too large")
+            f32 = dict(dtype=torch.float32, device=dev)
+            self.max_candidates = MC
+            self.cum = torch.zeros(B, **f32)
+            self.indir = torch.zeros((B, self.self_ld), dtype=torch.uint8, device=dev)
+            self.cand_score = torch.zeros((B, K + 1), **f32)
+            self.cand_tok = torch.zeros((B, K + 1), **i32)
+            self.fin_tokens = torch.zeros((NW, MC, self.max_len), **i32)
+            self.fin_score = torch.zeros((NW, MC), **f32)
+            self.fin_len = torch.zeros((NW, MC), **i32)
+            self.n_fin = torch.zeros(NW, **i32)
+            self.stream_done = torch.zeros(NW, dtype=torch.uint8, device=dev)
+            self.best_tokens = torch.zeros((NW, self.max_len), **i32)
+            self.best_score = torch.zeros(NW, **f32)
+            self.best_len = torch.zeros(NW, **i32)
+            self._cum0 = torch.full((NW, K), float("-inf"), **f32)
+            self._cum0[:, 0] = 0.0
+            self._cum0 = self._cum0.reshape(-1)
+            self._indir0 = (torch.arange(B, device=dev) % K).to(torch.uint8)[:, None].expand(B, self.self_ld).contiguous()
+            bs = BeamStateStruct()
+            bs.beam, bs.n_streams, bs.max_candidates = K, NW, MC
+            for name in ("cum", "indir", "cand_score", "cand_tok", "fin_tokens", "fin_score", "fin_len", "n_fin",
+                         "stream_done"):
+                setattr(bs, name, getattr(self, name).data_ptr())
+            self.beam_state = bs
         self.use_graph = use_graph
         self.graph: torch.cuda.CUDAGraph | None = None
         self.n_steps = self.n_prompt + self.max_new - 1
@@ -268,11 +312,26 @@ class DecodeSession:
         # embed, final LN, logits, pick, advance + 11 per layer; fused: embed, (segment + cross-attn) per layer,
         # final segment, logits, pick, advance
         self.kernels_per_step = (1 + 2 * L + 1 + 3) if fused else (3 + (13 if latent else 11) * L + 2 + 1)
+        if beam:
+            self.kernels_per_step += 1   # candidates + update instead of pick
 
     def _step(self) -> None:
         e = self.eng
+        if self.beam_state is not None:
+            _abi.call("janus_whisper_decode_beam_step", C.byref(e.c_dec_dims), C.byref(e.dec_weights),
+                      C.byref(self.state), C.byref(self.beam_state), torch.cuda.current_stream(e.device).cuda_stream)
+            return
         _abi.call("janus_whisper_decode_step", C.byref(e.c_dec_dims), C.byref(e.dec_weights), C.byref(self.state),
                   torch.cuda.current_stream(e.device).cuda_stream)
+
+    def finalize(self):
+        """Beam search: ranks every window's finished / live hypotheses (score / n_tokens) into best_tokens /
+        best_score / best_len. Enqueued on the current stream."""
+        e = self.eng
+        _abi.call("janus_whisper_beam_finalize", C.byref(self.state), C.byref(self.beam_state), e.spec.eot,
+                  self.best_tokens.data_ptr(), self.best_score.data_ptr(), self.best_len.data_ptr(),
+                  torch.cuda.current_stream(e.device).cuda_stream)
+        return self.best_tokens[:, self.n_prompt:], self.best_score
 
     def reset(self, forced: torch.Tensor | None = None) -> None:
         self.tokens.zero_()
@@ -286,6 +345,13 @@ class DecodeSession:
         self.n_done.zero_()
         self.sum_logprob.zero_()
         self.logprob.zero_()
+        if self.beam_state is not None:
+            if forced is not None:
+                raise ValueError("teacher forcing is a greedy-session feature")
+            self.cum.copy_(self._cum0)
+            self.indir.copy_(self._indir0)
+            self.n_fin.zero_()
+            self.stream_done.zero_()
 
     def enc_target(self) -> torch.Tensor | None:
         """Latent sessions read the encoder states during the whole decode: the buffer the encoder should write
@@ -294,13 +360,13 @@ class DecodeSession:
 
     def cross_kv(self, enc_out: torch.Tensor) -> None:
         e = self.eng
-        assert enc_out.shape[0] == self.B and enc_out.dtype == torch.bfloat16 and enc_out.is_contiguous()
+        assert enc_out.shape[0] == self.n_windows and enc_out.dtype == torch.bfloat16 and enc_out.is_contiguous()
         if self.latent:
             if enc_out.data_ptr() != self.enc_buf.data_ptr():
                 self.enc_buf.copy_(enc_out)
             return
         _abi.call("janus_whisper_cross_kv_bf16", C.byref(e.c_dec_dims), C.byref(e.dec_weights), enc_out.data_ptr(),
-                  self.B, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
+                  self.n_windows, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
                   torch.cuda.current_stream(e.device).cuda_stream)
 
     def _ensure_graph(self) -> None:
@@ -340,9 +406,12 @@ class DecodeSession:
                     self._step()
 
     def decode(self, enc_out: torch.Tensor, forced: torch.Tensor | None = None, n_steps: int | None = None):
-        """Returns (tokens [B, max_new] int32 device, sum_logprob [B]). Does not synchronise."""
+        """Returns (tokens [n_windows, max_new] int32 device, sum_logprob [n_windows]); with beam search those of the
+        best hypothesis of every window. Does not synchronise."""
         self._ensure_graph()
         self.cross_kv(enc_out)
         self.reset(forced)
         self.run_steps(n_steps)
+        if self.beam_state is not None:
+            return self.finalize()
         return self.tokens[:, self.n_prompt:], self.sum_logprob

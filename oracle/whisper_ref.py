@@ -189,3 +189,105 @@ def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tens
     if return_margins:
         return out, sum_lp, margins
     return out, sum_lp
+
+
+# ----------------------------------------------------------------------------------------------
+# beam search (BASELINE configs[3]: beam 5; the reference's own call uses beam_size=1, transcriber.py:55)
+# ----------------------------------------------------------------------------------------------
+def beam_step_select(cand: list[tuple[float, int, int]], beam_size: int, eot: int):
+    """One stream, one step of the beam bookkeeping. `cand` = (score, beam, token) for the top
+    beam_size + 1 tokens of every live beam. Walk the candidates by descending score (ties: beam, then
+    token ascending; a score of -inf is no candidate): eot candidates finish their hypothesis, the first
+    `beam_size` others become the next beams; slots left over are dead beams (score -inf, their own history,
+    token eot). Returns (next beams [(score, parent, token)], newly finished [(score, parent)])."""
+    order = sorted(cand, key=lambda c: (-c[0], c[1], c[2]))
+    nxt, fin = [], []
+    for s, k, t in order:
+        if s == float("-inf"):
+            break
+        if t == eot:
+            fin.append((s, k))
+        else:
+            nxt.append((s, k, t))
+            if len(nxt) == beam_size:
+                break
+    while len(nxt) < beam_size:
+        nxt.append((float("-inf"), len(nxt), eot))
+    return nxt, fin
+
+
+def beam_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor, max_new_tokens: int,
+                beam_size: int = 5, patience: float = 1.0, return_all: bool = False):
+    """Beam search at temperature 0 as published in OpenAI Whisper's `BeamSearchDecoder.update/finalize` +
+    `MaximumLikelihoodRanker(length_penalty=None)` -- the algorithm faster-whisper / CTranslate2 run for
+    `beam_size=5, patience=1, length_penalty=1` (PARITY UNPINNED against CTranslate2, see the module header):
+
+    * per live beam the rule-filtered log-softmax; candidates = its top beam_size+1 tokens, score = cumulative
+      log-prob + token log-prob; the beams of a stream are identical before the first sampled token, so only
+      beam 0 is live there (cumulative score -inf for the others: same effect as the dict de-duplication);
+    * beam_step_select(); newly finished hypotheses join the stream's finished list in descending score while
+      it holds fewer than max_candidates = round(beam_size * patience); a stream is complete when it is full;
+    * at the end a stream with fewer than beam_size finished hypotheses adds its live beams by descending
+      cumulative score; the result is the hypothesis with the largest score / n_tokens (tokens before eot).
+
+    Returns tokens [B, max_new_tokens] (eot-padded), sum_logprob [B] of the chosen hypothesis; with
+    return_all also the per-stream ranking pools and finished lists [(tokens, score, length)]."""
+    B, K = enc_out.shape[0], beam_size
+    max_cand = int(round(beam_size * patience))
+    eot = spec.eot
+    st = DecoderState(W, dims, enc_out.repeat_interleave(K, 0))
+    sup = suppress_mask_for(spec)
+    prompt = torch.tensor([list(spec.sot_sequence)] * (B * K), dtype=torch.long)
+    logits = st.step(prompt)[:, -1]
+    gen = [[[] for _ in range(K)] for _ in range(B)]
+    cum = [[0.0] + [float("-inf")] * (K - 1) for _ in range(B)]
+    finished = [[] for _ in range(B)]     # (tokens, score, length)
+    n_steps = min(max_new_tokens, spec.max_length - len(spec.sot_sequence))
+    f32 = lambda v: float(torch.as_tensor(v, dtype=torch.float32))
+    for t in range(n_steps):
+        src = torch.arange(B * K)
+        nxt_tok = torch.full((B * K,), eot, dtype=torch.long)
+        for b in range(B):
+            if len(finished[b]) >= max_cand:
+                continue
+            cand = []
+            for k in range(K):
+                lg = apply_logit_rules(logits[b * K + k], gen[b][k], spec, sup)
+                lp = torch.log_softmax(lg, dim=-1)
+                v, i = torch.sort(lp, descending=True, stable=True)
+                for r in range(K + 1):
+                    cand.append((f32(torch.tensor(cum[b][k], dtype=torch.float32) + v[r]), k, int(i[r])))
+            nxt, fin = beam_step_select(cand, K, eot)
+            for s, k in fin:
+                if len(finished[b]) < max_cand:
+                    finished[b].append((list(gen[b][k]), s, len(gen[b][k])))
+            new_gen, new_cum = [], []
+            for j, (s, k, tok) in enumerate(nxt):
+                new_gen.append(gen[b][k] + [tok])
+                new_cum.append(s)
+                src[b * K + j] = b * K + k
+                nxt_tok[b * K + j] = tok
+            gen[b], cum[b] = new_gen, new_cum
+        if all(len(f) >= max_cand for f in finished) or t == n_steps - 1:
+            break
+        for i in range(dims.n_text_layer):
+            st.self_kv[i] = (st.self_kv[i][0][src], st.self_kv[i][1][src])
+        logits = st.step(nxt_tok[:, None])[:, -1]
+    out = torch.full((B, max_new_tokens), eot, dtype=torch.long)
+    sum_lp = torch.zeros(B)
+    pools = []
+    for b in range(B):
+        pool = list(finished[b])
+        if len(pool) < K:
+            for k in sorted(range(K), key=lambda k: (-cum[b][k], k)):
+                pool.append((list(gen[b][k]), cum[b][k], len(gen[b][k])))
+                if len(pool) >= K:
+                    break
+        best = max(range(len(pool)), key=lambda j: (f32(pool[j][1]) / max(pool[j][2], 1), -j))
+        toks = pool[best][0][:max_new_tokens]
+        out[b, :len(toks)] = torch.tensor(toks, dtype=torch.long)
+        sum_lp[b] = pool[best][1]
+        pools.append(pool)
+    if return_all:
+        return out, sum_lp, pools, finished
+    return out, sum_lp

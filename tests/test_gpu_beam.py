@@ -1,0 +1,151 @@
+"""K3 beam search on a real B200 (through the C ABI: janus_whisper_decode_beam_step / janus_whisper_beam_finalize)
+vs the fp32 CPU oracle's beam_decode (oracle/whisper_ref.py).
+
+Stated bars:
+  * beam = 1 is the greedy decoder: tokens bit-identical to the greedy session of the same engine;
+  * "confident" weights (margins >> bf16 noise): the best hypothesis of every window equals the oracle's wherever
+    the oracle's best / second-best normalised scores differ by more than SCORE_MARGIN, its sum of log-probs is
+    within LP_TOL, and the list of finished hypotheses (tokens, order, lengths) equals the oracle's wherever the
+    scores that ordered it are SCORE_MARGIN apart;
+  * the grouped latent cross-attention (beams sharing one window of encoder states) is bit-identical to the
+    ungrouped kernel on replicated encoder states.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+SCORE_MARGIN = 0.05
+LP_TOL = 0.15
+
+
+def _setup(eot_scale=None, d=128, heads=2, layers=2, n_clips=3, seed=3):
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.engine import WhisperEngine
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = test_dims(d=d, heads=heads, layers=layers)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=seed, profile="confident")
+    if eot_scale is not None:
+        # make <|endoftext|> a strong runner-up of the most frequent token so that hypotheses finish at different
+        # lengths, finished lists fill up and windows complete early
+        with torch.no_grad():
+            clips0 = make_clips(1, 30.0, 16000, seed=77).numpy()
+            mel0 = torch.from_numpy(log_mel_window(clips0[0], dims.n_mels))[None]
+            g, _ = R.greedy_decode(W, dims, spec, R.encode(W, dims, mel0), 4)
+        frequent = int(g[0, 1])
+        E = W["dec.tok_emb"].clone()
+        E[spec.eot] = (eot_scale * E[frequent]).to(torch.bfloat16).float()
+        W = dict(W)
+        W["dec.tok_emb"] = E
+    clips = make_clips(n_clips, 30.0, 16000, seed=77).numpy()
+    mel = torch.stack([torch.from_numpy(log_mel_window(c, dims.n_mels)) for c in clips])
+    with torch.no_grad():
+        enc_ref = R.encode(W, dims, mel)
+    eng = WhisperEngine(dims, W, torch.device("cuda", 0))
+    return dims, spec, W, enc_ref, eng, R
+
+
+@pytest.mark.parametrize("latent", [False, True])
+def test_beam1_is_greedy(latent):
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, enc_ref, eng, R = _setup()
+    enc = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    n_new = 24
+    g = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=n_new, latent=latent)
+    gt, glp = g.decode(enc)
+    b = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=n_new, latent=latent, beam=1)
+    bt, blp = b.decode(enc)
+    torch.cuda.synchronize()
+    assert torch.equal(gt.cpu(), bt.cpu())
+    assert torch.allclose(glp.cpu(), blp.cpu(), atol=1e-3)
+
+
+def _norm(score, length):
+    return score / max(length, 1)
+
+
+@pytest.mark.parametrize("latent,eot_scale,use_graph", [(False, None, True), (True, None, True), (False, 0.9, False),
+                                                        (True, 0.9, True)])
+def test_beam5_vs_oracle(latent, eot_scale, use_graph):
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, enc_ref, eng, R = _setup(eot_scale)
+    n_new, K = 16, 5
+    with torch.no_grad():
+        ref_tok, ref_lp, pools, finished = R.beam_decode(W, dims, spec, enc_ref, n_new, beam_size=K, return_all=True)
+    enc = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    ses = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=n_new, latent=latent, beam=K, use_graph=use_graph,
+                        steps_per_graph=4)
+    assert ses.latent == latent
+    for rep in range(2):   # the second decode reuses the session (reset of cum / indirection / finished lists)
+        tok, lp = ses.decode(enc)
+        torch.cuda.synchronize()
+        tok, lp = tok.cpu().long(), lp.cpu()
+        n_fin = ses.n_fin.cpu().tolist()
+        checked = 0
+        for b in range(enc.shape[0]):
+            pool = pools[b]
+            ranked = sorted((_norm(p[1], p[2]) for p in pool), reverse=True)
+            if len(ranked) < 2 or ranked[0] - ranked[1] > SCORE_MARGIN:
+                assert tok[b].tolist() == ref_tok[b].tolist(), (b, tok[b].tolist(), ref_tok[b].tolist())
+                assert abs(float(lp[b]) - float(ref_lp[b])) <= LP_TOL
+                checked += 1
+            # finished hypotheses: the oracle's pool lists them first, in the order they finished
+            fin_ref = finished[b]
+            if eot_scale is not None:
+                fs = ses.fin_score[b].cpu().tolist()
+                fl = ses.fin_len[b].cpu().tolist()
+                ft = ses.fin_tokens[b].cpu().tolist()
+                scores = [p[1] for p in fin_ref]
+                distinct = all(abs(scores[i] - scores[j]) > SCORE_MARGIN for i in range(len(scores))
+                               for j in range(i + 1, len(scores)))
+                if distinct and len(fin_ref) == n_fin[b]:
+                    for j, p in enumerate(fin_ref):
+                        assert fl[j] == p[2], (b, j, fl, [q[2] for q in fin_ref])
+                        assert ft[j][ses.n_prompt:ses.n_prompt + p[2]] == p[0], (b, j)
+                        assert ft[j][ses.n_prompt + p[2]] == spec.eot
+                        assert abs(fs[j] - p[1]) <= LP_TOL
+        assert checked >= 1, "no window had a decisive best hypothesis: the test checked nothing"
+        if eot_scale is not None:
+            assert sum(n_fin) > 0, "the eot-biased weights were meant to finish hypotheses"
+            done = ses.stream_done.cpu().tolist()
+            assert [int(n >= K) for n in n_fin] == done
+
+
+def test_beam_latent_equals_kv_form():
+    """Device against device at Whisper-tiny width (d = 384, 6 heads): the two cross-attention forms pick the same
+    best hypothesis under beam search."""
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, enc_ref, eng, R = _setup(0.9, d=384, heads=6, layers=2, n_clips=4)
+    enc = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    out = []
+    for latent in (False, True):
+        ses = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=12, latent=latent, beam=5)
+        tok, lp = ses.decode(enc)
+        torch.cuda.synchronize()
+        out.append((tok.cpu(), lp.cpu(), ses.best_len.cpu()))
+    assert torch.equal(out[0][0], out[1][0])
+    assert torch.equal(out[0][2], out[1][2])
+    assert torch.allclose(out[0][1], out[1][1], atol=LP_TOL)
+
+
+@pytest.mark.parametrize("n_streams,group,T,d,H", [(7, 5, 1500, 768, 12), (40, 5, 300, 768, 12), (6, 4, 200, 384, 6),
+                                                   (31, 5, 500, 1024, 16)])
+def test_xlat_grouped_is_bit_identical(n_streams, group, T, d, H):
+    from janus_b200 import _abi
+    g = torch.Generator(device="cuda").manual_seed(11)
+    n = n_streams * group
+    enc = torch.randn(n_streams, T, d, device="cuda", generator=g).bfloat16()
+    qlat = torch.zeros(n, 16, d, device="cuda", dtype=torch.bfloat16)
+    qlat[:, :H] = (torch.randn(n, H, d, device="cuda", generator=g) * (8.0 / d ** 0.5)).bfloat16()
+    z1 = torch.full((n, H, d), float("nan"), device="cuda", dtype=torch.bfloat16)
+    z2 = torch.full((n, H, d), float("nan"), device="cuda", dtype=torch.bfloat16)
+    st = torch.cuda.current_stream().cuda_stream
+    _abi.call("janus_dec_xlat_grouped_bf16", qlat.data_ptr(), enc.data_ptr(), z1.data_ptr(), n, group, T, d, H, st)
+    rep = enc.repeat_interleave(group, 0).contiguous()
+    _abi.call("janus_dec_xlat_bf16", qlat.data_ptr(), rep.data_ptr(), z2.data_ptr(), n, T, d, H, st)
+    torch.cuda.synchronize()
+    assert torch.isfinite(z1.float()).all()
+    assert torch.equal(z1, z2)

@@ -124,3 +124,38 @@ def test_presets_param_counts():
         enc = d.n_mels * n * 3 + n + 3 * n * n + n + d.n_audio_layer * (4 * n * n + 3 * n + 8 * n * n + 5 * n + 4 * n) + 2 * n
         dec = d.n_vocab * n + 448 * n + d.n_text_layer * (8 * n * n + 6 * n + 8 * n * n + 5 * n + 6 * n) + 2 * n
         assert lo < enc + dec < hi, (name, enc + dec)
+
+
+def test_beam_oracle_beam1_is_greedy_and_beam5_never_scores_lower():
+    """oracle/whisper_ref.py beam_decode: beam 1 reproduces greedy_decode; the best of 5 beams has a normalised
+    score >= the greedy hypothesis (same length here: random weights do not emit eot)."""
+    import torch
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    dims = test_dims(d=64, heads=1, layers=1)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=5, profile="diverse")
+    torch.manual_seed(0)
+    enc = torch.randn(2, dims.n_audio_ctx, dims.n_audio_state) * 0.5
+    with torch.no_grad():
+        g, glp = R.greedy_decode(W, dims, spec, enc, 6)
+        b1, b1lp = R.beam_decode(W, dims, spec, enc, 6, beam_size=1)
+        b5, b5lp = R.beam_decode(W, dims, spec, enc, 6, beam_size=5)
+    assert torch.equal(g, b1) and torch.allclose(glp, b1lp, atol=1e-4)
+    assert bool((b5lp >= glp - 1e-4).all())
+
+
+def test_beam_step_select_walk():
+    """The published walk: eot candidates finish, the first `beam` others continue, -inf is no candidate."""
+    from oracle.whisper_ref import beam_step_select
+    eot = 9
+    ninf = float("-inf")
+    cand = [(-1.0, 0, 3), (-1.5, 0, eot), (-2.0, 0, 4), (-0.5, 1, eot), (-1.2, 1, 7), (-3.0, 1, 2),
+            (ninf, 2, 1), (ninf, 2, eot), (ninf, 2, 5)]
+    nxt, fin = beam_step_select(cand, 3, eot)
+    assert fin == [(-0.5, 1), (-1.5, 0)]
+    assert nxt == [(-1.0, 0, 3), (-1.2, 1, 7), (-2.0, 0, 4)]
+    # fewer live candidates than beams: the remaining slots are dead beams
+    nxt, fin = beam_step_select([(-1.0, 0, 3), (ninf, 1, 4), (ninf, 1, 5)], 2, eot)
+    assert nxt == [(-1.0, 0, 3), (ninf, 1, eot)] and fin == []
