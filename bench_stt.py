@@ -232,6 +232,10 @@ def run_gpu_stt(args) -> None:
                 elif latent:
                     _abi.call("janus_dec_xlat_bf16", s_.qlat.data_ptr(), s_.enc_buf.data_ptr(), s_.zlat.data_ptr(), lb,
                               d.n_audio_ctx, d.n_text_state, d.n_text_head, stream.cuda_stream)
+                elif beam > 1:   # one pass over K / V serves the beams of a window
+                    _abi.call("janus_dec_cross_attn_beam_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(),
+                              s_.cross_v[l].data_ptr(), s_.att.data_ptr(), lb, beam, d.n_text_head, d.n_audio_ctx,
+                              enc.whisper.kv_ld, stream.cuda_stream)
                 else:
                     _abi.call("janus_dec_cross_attn_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(),
                               s_.cross_v[l].data_ptr(), s_.att.data_ptr(), lb, d.n_text_head, d.n_audio_ctx,
@@ -299,7 +303,7 @@ def run_gpu_stt(args) -> None:
         if latent:   # the encoder states of every window once, absorbed queries (16 rows) in, z out
             alg_bytes = lb * T * d.n_text_state * 2 + lb * beam * (16 + H) * d.n_text_state * 2
         else:
-            alg_bytes = lb * H * (2 * T * 64 * 2) + 2 * lb * d.n_text_state * 2
+            alg_bytes = lb * H * (2 * T * 64 * 2) + 2 * lb * beam * d.n_text_state * 2
         achieved = alg_bytes / (xattn_ms / 1e3) / 1e9
         # encoder tensor-pipe figure for context (SURVEY 8d FLOP count)
         dd, L, Ta = d.n_audio_state, d.n_audio_layer, d.n_audio_ctx
@@ -322,7 +326,7 @@ def run_gpu_stt(args) -> None:
                     "packets_per_step": n_pkts * world},
             "gpu_launches": enc.kernels_per_step() * args.steps,
             "stages_ms": stages,
-            "roofline": {"kernel": "dec_xlat_kernel" if latent else "dec_cross_attn_kernel", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+            "roofline": {"kernel": "dec_xlat_kernel" if latent else ("dec_cross_attn_beam_kernel" if beam > 1 else "dec_cross_attn_kernel"), "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                          "note": ("cross-attention over the encoder states themselves (K/V projections absorbed into "
                                   "the query / output sides): half the bytes of the K/V-cache kernel per launch"

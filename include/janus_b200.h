@@ -298,6 +298,13 @@ int32_t janus_whisper_decode_beam_step(const janus_whisper_dims_t* dims, const j
  * eot padding), best_score [n_streams] sum of log-probs, best_len [n_streams] sampled tokens before eot. */
 int32_t janus_whisper_beam_finalize(const janus_decode_state_t* state, const janus_beam_state_t* beam, int32_t eot,
                                     int32_t* best_tokens, float* best_score, int32_t* best_len, void* stream);
+/* One layer of decode-time cross-attention for beam search, K/V-cache form: the `beam` rows of a stream (row = stream
+ * * beam + k) attend to the same K / V, which one CTA per (stream, head) streams once for all of them.
+ * q / out bf16 [n_streams * beam, 64 * n_heads]; cross_k / cross_v as in janus_dec_cross_attn_bf16 with batch =
+ * n_streams; 2 <= beam <= JANUS_MAX_BEAM. */
+int32_t janus_dec_cross_attn_beam_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
+                                       int32_t n_streams, int32_t beam, int32_t n_heads, int32_t n_ctx, int32_t kv_ld,
+                                       void* stream);
 /* janus_dec_xlat_bf16 for rows that share encoder states in groups (beam search): qlat [n_rows, 16, d],
  * enc [n_rows / group, n_ctx, d], z [n_rows, n_heads, d]. */
 int32_t janus_dec_xlat_grouped_bf16(const void* qlat, const void* enc, void* z, int32_t n_rows, int32_t group,

@@ -168,7 +168,7 @@ constexpr int XA_THREADS = 192;  // 192 * 8 keys = 1536 >= 1500
 __global__ void __launch_bounds__(XA_THREADS)
 dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kT,
                       const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, int H, int n_items,
-                      __nv_bfloat16* out, int kv_group) {
+                      __nv_bfloat16* out) {
   // 6.4 KB of shared memory and 40 registers per thread: with the grid capped at 3 CTAs per SM (xa_grid)
   // three of these fit beside one persistent tcgen05 GEMM CTA of the encoder stream (198 KB, 41 K registers)
   __shared__ float qs[DH];
@@ -180,7 +180,7 @@ dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ 
   pdl_wait();
   for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
   const int b = item / H, h = item - b * H;
-  const long long bh = (long long)(b / kv_group) * H + h;   // kv_group beams of a stream share its K/V (L2 hits)
+  const long long bh = (long long)b * H + h;
   if (tid < DH) qs[tid] = __bfloat162float(q[(long long)b * d + h * DH + tid]) * (0.125f * 1.4426950408889634f);
   __syncthreads();
   // ---- scores for keys 8*tid .. 8*tid+7
@@ -271,6 +271,182 @@ static int xa_grid(int n_items) {
   if (cap <= 0) return n_items;
   const long long g = (long long)cap * num_sms();
   return n_items < g ? n_items : (int)g;
+}
+
+// ------------------------------------------------------------------------------------------
+// cross-attention for beam search: the NQ beams of a stream attend to the same K / V, so one CTA per
+// (stream, head) streams them ONCE and serves all NQ queries (NQ x the FMAs per byte; still HBM-bound: 64 dims x
+// NQ FMAs per 16-byte load). Same layouts and thread mapping as dec_cross_attn_kernel.
+// ------------------------------------------------------------------------------------------
+// FMAs are issued as packed fp32 pairs (fma.rn.f32x2: half the issue slots of 40 scalar FMAs per 16-byte load; the
+// kernel is issue- / latency-bound, not FMA-pipe-bound); US / UV = unroll of the two streaming loops (the compiler
+// software-pipelines the loads across the unrolled bodies). Measured at 512 streams x 12 heads x 5 beams (2.37 GB per
+// launch, scripts/gpu_xb_bench.py): scalar FMAs 3.6-3.7 TB/s; packed 4.57 (US / UV = 8 / 4) - 4.72 TB/s (16 / 8) at 96
+// registers, 3 CTAs per SM; gathering a batch of loads up front 3.2-4.3; forcing 4 / 5 CTAs per SM through
+// __launch_bounds__ 4.0 / 2.3 (spills), 2 CTAs with 140 registers 4.1; a larger shared-memory carve-out does not help.
+template <int NQ, int US, int UV>
+__global__ void __launch_bounds__(XA_THREADS)
+dec_cross_attn_beam_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kT,
+                           const __nv_bfloat16* __restrict__ v, int T, int kv_ld, int d, int H, int n_items,
+                           __nv_bfloat16* out) {
+  extern __shared__ __align__(16) float xb_smem[];
+  float (*ps)[XA_THREADS * 8] = reinterpret_cast<float (*)[XA_THREADS * 8]>(xb_smem);   // [NQ][1536]
+  __shared__ __align__(8) float2 qs[NQ][DH];   // (q, q): one 8-byte load gives the packed multiplier
+  __shared__ float wred[2][NQ][XA_THREADS / 32];
+  const int tid = threadIdx.x;
+  pdl_launch_dependents();
+  pdl_wait();
+  for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+  const int b = item / H, h = item - b * H;   // b: stream; its rows are b * NQ .. b * NQ + NQ - 1
+  const long long bh = (long long)b * H + h;
+  for (int i = tid; i < NQ * DH; i += XA_THREADS) {
+    const int qi = i / DH, e = i - qi * DH;
+    const float x = __bfloat162float(q[((long long)b * NQ + qi) * d + h * DH + e]) * (0.125f * 1.4426950408889634f);
+    qs[qi][e] = make_float2(x, x);
+  }
+  __syncthreads();
+  const int key0 = tid * 8;
+  uint64_t acc2[NQ][4];
+#pragma unroll
+  for (int qi = 0; qi < NQ; ++qi)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc2[qi][i] = 0ull;
+  if (key0 < T) {
+    const uint4* kp = reinterpret_cast<const uint4*>(kT + bh * DH * kv_ld + key0);
+    const int stride = kv_ld >> 3;
+#pragma unroll US
+    for (int dim = 0; dim < DH; ++dim) {
+      const uint4 u = __ldg(kp + (long long)dim * stride);
+      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+      uint64_t f2[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 t2 = __bfloat1622float2(hh[e]);
+        f2[e] = pack_f32x2(t2.x, t2.y);
+      }
+#pragma unroll
+      for (int qi = 0; qi < NQ; ++qi) {
+        const uint64_t qd = *reinterpret_cast<const uint64_t*>(&qs[qi][dim]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc2[qi][e] = fma_f32x2(f2[e], qd, acc2[qi][e]);
+      }
+    }
+  }
+#pragma unroll
+  for (int qi = 0; qi < NQ; ++qi) {
+    float a[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) unpack_f32x2(acc2[qi][e], a[2 * e], a[2 * e + 1]);
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a[i] = (key0 + i < T) ? a[i] : -INFINITY;
+      mx = fmaxf(mx, a[i]);
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) acc2[qi][e] = pack_f32x2(a[2 * e], a[2 * e + 1]);
+    mx = warp_max(mx);
+    if ((tid & 31) == 0) wred[0][qi][tid >> 5] = mx;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int qi = 0; qi < NQ; ++qi) {
+    float m = wred[0][qi][0];
+#pragma unroll
+    for (int w = 1; w < XA_THREADS / 32; ++w) m = fmaxf(m, wred[0][qi][w]);
+    float sm = 0.f;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float a0, a1;
+      unpack_f32x2(acc2[qi][e], a0, a1);
+      const float p0 = exp2f(a0 - m), p1 = exp2f(a1 - m);
+      *reinterpret_cast<float2*>(&ps[qi][key0 + 2 * e]) = make_float2(p0, p1);
+      sm += p0;
+      sm += p1;
+    }
+    sm = warp_sum(sm);
+    if ((tid & 31) == 0) wred[1][qi][tid >> 5] = sm;
+  }
+  __syncthreads();
+  // ---- PV: 8 lanes per 128-byte V row, 24 rows per pass, every row used by all NQ queries
+  const int c = tid & 7, rg = tid >> 3;
+  uint64_t o2[NQ][4];
+#pragma unroll
+  for (int qi = 0; qi < NQ; ++qi)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o2[qi][i] = 0ull;
+  const uint4* vp = reinterpret_cast<const uint4*>(v + bh * (long long)T * DH) + c;
+#pragma unroll UV
+  for (int j = rg; j < T; j += XA_THREADS / 8) {
+    const uint4 u = __ldg(vp + (long long)j * 8);
+    const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+    uint64_t f2[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 t2 = __bfloat1622float2(hh[e]);
+      f2[e] = pack_f32x2(t2.x, t2.y);
+    }
+#pragma unroll
+    for (int qi = 0; qi < NQ; ++qi) {
+      const float p = ps[qi][j];
+      const uint64_t pp = pack_f32x2(p, p);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o2[qi][e] = fma_f32x2(f2[e], pp, o2[qi][e]);
+    }
+  }
+  __syncthreads();   // every thread is done reading ps: reuse each query's region for its cross-row reduction
+#pragma unroll
+  for (int qi = 0; qi < NQ; ++qi)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float o0, o1;
+      unpack_f32x2(o2[qi][e], o0, o1);
+      *reinterpret_cast<float2*>(&ps[qi][rg * DH + c * 8 + 2 * e]) = make_float2(o0, o1);
+    }
+  __syncthreads();
+  for (int i = tid; i < NQ * DH; i += XA_THREADS) {
+    const int qi = i / DH, e = i - qi * DH;
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < XA_THREADS / 8; ++r) t += ps[qi][r * DH + e];
+    float sm = 0.f;
+#pragma unroll
+    for (int w = 0; w < XA_THREADS / 32; ++w) sm += wred[1][qi][w];
+    out[((long long)b * NQ + qi) * d + h * DH + e] = __float2bfloat16_rn(t / sm);
+  }
+  __syncthreads();   // qs / ps / wred are rewritten by the next item
+  }
+}
+
+template <int NQ, int US, int UV>
+static int launch_cross_attn_beam(const __nv_bfloat16* q, const __nv_bfloat16* kT, const __nv_bfloat16* v, int T, int kv_ld,
+                                  int d, int H, int n_streams, __nv_bfloat16* out, cudaStream_t st) {
+  const size_t smem = (size_t)NQ * XA_THREADS * 8 * sizeof(float);
+  static bool attr = false;
+  if (!attr) {
+    JANUS_CUDA(cudaFuncSetAttribute(dec_cross_attn_beam_kernel<NQ, US, UV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)smem));
+    attr = true;
+  }
+  JANUS_CUDA(launch_pdl(dec_cross_attn_beam_kernel<NQ, US, UV>, dim3(xa_grid(H * n_streams)), dim3(XA_THREADS), smem, st, q,
+                        kT, v, T, kv_ld, d, H, H * n_streams, out));
+  return JANUS_OK;
+}
+
+// q / out: [n_streams * beam, d] (row = stream * beam + k); kT / v: one layer's cross K / V of n_streams streams
+static int dec_cross_attn_beam(const __nv_bfloat16* q, const __nv_bfloat16* kT, const __nv_bfloat16* v, int T, int kv_ld,
+                               int d, int H, int n_streams, int beam, __nv_bfloat16* out, cudaStream_t st) {
+  switch (beam) {
+    case 2: return launch_cross_attn_beam<2, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    case 3: return launch_cross_attn_beam<3, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    case 4: return launch_cross_attn_beam<4, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    case 5: return launch_cross_attn_beam<5, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    case 6: return launch_cross_attn_beam<6, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    case 7: return launch_cross_attn_beam<7, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    case 8: return launch_cross_attn_beam<8, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
+    default: JANUS_CHECK_ARG(false, "cross_attn_beam: beam=%d unsupported", beam);
+  }
+  return JANUS_OK;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -457,9 +633,21 @@ extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k,
   dec_cross_attn_kernel<<<xa_grid(n_heads * batch), XA_THREADS, 0, (cudaStream_t)stream>>>(
       static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(cross_k),
       static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, n_heads, n_heads * batch,
-      static_cast<__nv_bfloat16*>(out), 1);
+      static_cast<__nv_bfloat16*>(out));
   JANUS_LAUNCH_CHECK("dec_cross_attn_kernel");
   return JANUS_OK;
+}
+
+extern "C" int32_t janus_dec_cross_attn_beam_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
+                                                  int32_t n_streams, int32_t beam, int32_t n_heads, int32_t n_ctx,
+                                                  int32_t kv_ld, void* stream) {
+  JANUS_CHECK_ARG(q && cross_k && cross_v && out && n_streams > 0 && n_heads > 0, "cross_attn_beam: bad argument");
+  JANUS_CHECK_ARG(beam >= 2 && beam <= JANUS_MAX_BEAM, "cross_attn_beam: beam=%d must be in 2 .. %d", beam, JANUS_MAX_BEAM);
+  JANUS_CHECK_ARG(n_ctx <= XA_THREADS * 8 && kv_ld % 8 == 0 && kv_ld >= n_ctx && kv_ld <= XA_THREADS * 8,
+                  "cross_attn_beam: n_ctx=%d / kv_ld=%d unsupported", n_ctx, kv_ld);
+  return dec_cross_attn_beam(static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(cross_k),
+                             static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, n_heads, n_streams,
+                             beam, static_cast<__nv_bfloat16*>(out), (cudaStream_t)stream);
 }
 
 extern "C" int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
@@ -553,7 +741,7 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
       if ((rc = dec_fused_segment(P, st))) return rc;
       JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                             static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att, 1));
+                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
     }
     FusedProgram P = base;
     tail_of(P, w->layers[c->n_layers - 1]);
@@ -604,9 +792,15 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
         if ((rc = gemm_bf16(zlat, (long long)H * d, d, static_cast<const __nv_bfloat16*>(L.w_cv), d, g, st))) return rc;
       }
     } else {
+    if (grp > 1) {   // beam search: one CTA per (stream, head) serves all beams from one pass over K / V
+      if ((rc = dec_cross_attn_beam(q, static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
+                                    static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H,
+                                    B / grp, grp, att, st))) return rc;
+    } else {
     JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                           static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att, grp));
+                          static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
+    }
     }
     if ((rc = linear(att, d, L.w_co, L.b_co, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
     if ((rc = layernorm_bf16(x, L.ln2_w, L.ln2_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;

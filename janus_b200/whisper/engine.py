@@ -236,7 +236,9 @@ class DecodeSession:
         self.self_k = torch.zeros((L, B, H, self.self_ld, 64), **bf)
         self.self_v = torch.zeros((L, B, H, self.self_ld, 64), **bf)
         if latent is None:
-            latent = engine.latent_ok and not light and not fused and NW >= self.LATENT_MIN_BATCH
+            # beam search defaults to the K/V-cache form: its kernel serves all beams of a window from ONE pass over
+            # K / V (4.6 MB per window and layer), while the latent kernel walks the encoder states once per beam
+            latent = engine.latent_ok and not light and not fused and NW >= self.LATENT_MIN_BATCH and beam <= 1
         if latent and not engine.latent_ok:
             raise ValueError("latent cross-attention needs d % 128 == 0, d <= 1024 and <= 16 heads")
         if latent and (light or fused):
