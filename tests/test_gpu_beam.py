@@ -156,3 +156,30 @@ def test_xlat_grouped_is_bit_identical(n_streams, group, T, d, H):
     torch.cuda.synchronize()
     assert torch.isfinite(z1.float()).all()
     assert torch.equal(z1, z2)
+
+
+@pytest.mark.parametrize("latent", [False, True])
+def test_beam5_many_windows_replica_property(latent):
+    """Size-independent property at a lane-sized batch (136 windows = 680 decode rows, tcgen05 GEMM path, latent form
+    at >= 128 windows): replicas of a window, scattered over the batch, must produce identical hypotheses, finished
+    lists and scores -- whatever their neighbours do to the shared buffers, the indirection and the reorder."""
+    from janus_b200.whisper.engine import DecodeSession
+    dims, spec, W, enc_ref, eng, R = _setup(0.9, d=384, heads=6, layers=2, n_clips=8)
+    n_rep = 17
+    idx = torch.arange(8).repeat(n_rep)[torch.randperm(8 * n_rep, generator=torch.Generator().manual_seed(1))]
+    enc = enc_ref.to(torch.bfloat16)[idx].cuda().contiguous()
+    ses = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=12, latent=latent, beam=5, steps_per_graph=5)
+    assert ses.latent == latent
+    tok, lp = ses.decode(enc)
+    torch.cuda.synchronize()
+    tok, lp, nf = tok.cpu(), lp.cpu(), ses.n_fin.cpu()
+    fin_t, fin_s = ses.fin_tokens.cpu(), ses.fin_score.cpu()
+    for w in range(8):
+        rows = (idx == w).nonzero().flatten().tolist()
+        r0 = rows[0]
+        for r in rows[1:]:
+            assert torch.equal(tok[r], tok[r0]) and float(lp[r]) == float(lp[r0]), (w, r)
+            assert int(nf[r]) == int(nf[r0])
+            n = int(nf[r0])
+            assert torch.equal(fin_t[r, :n], fin_t[r0, :n]) and torch.equal(fin_s[r, :n], fin_s[r0, :n])
+    assert int(nf.sum()) > 0
