@@ -235,7 +235,7 @@ def run_gpu_stt(args) -> None:
                 elif beam > 1:   # one pass over K / V serves the beams of a window
                     _abi.call("janus_dec_cross_attn_beam_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(),
                               s_.cross_v[l].data_ptr(), s_.att.data_ptr(), lb, beam, d.n_text_head, d.n_audio_ctx,
-                              enc.whisper.kv_ld, stream.cuda_stream)
+                              enc.whisper.kv_ld, 1, stream.cuda_stream)
                 else:
                     _abi.call("janus_dec_cross_attn_bf16", s_.q.data_ptr(), s_.cross_k[l].data_ptr(),
                               s_.cross_v[l].data_ptr(), s_.att.data_ptr(), lb, d.n_text_head, d.n_audio_ctx,
@@ -326,7 +326,7 @@ def run_gpu_stt(args) -> None:
                     "packets_per_step": n_pkts * world},
             "gpu_launches": enc.kernels_per_step() * args.steps,
             "stages_ms": stages,
-            "roofline": {"kernel": "dec_xlat_kernel" if latent else ("dec_cross_attn_beam_kernel" if beam > 1 else "dec_cross_attn_kernel"), "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+            "roofline": {"kernel": "dec_xlat_kernel" if latent else ("dec_cross_attn_beam_mma_kernel" if beam > 1 else "dec_cross_attn_kernel"), "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
                          "note": ("cross-attention over the encoder states themselves (K/V projections absorbed into "
                                   "the query / output sides): half the bytes of the K/V-cache kernel per launch"

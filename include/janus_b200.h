@@ -206,6 +206,11 @@ typedef struct {
  * caches -- half the HBM bytes per step, no cross_k / cross_v at all (janus_b200/csrc/dec_xlat.cu). Needs
  * d % 128 == 0, d <= 1024, <= 16 heads, the w_ck_lat / w_cv / b_cv layer weights and state->enc_out / qlat / zlat. */
 #define JANUS_DECODE_LATENT 4
+/* JANUS_DECODE_KV_SWAPPED (beam search, K/V-cache form): the two cross-attention cache layouts swap roles --
+ * cross_k bf16 [L, n_streams, H, n_ctx, 64] (row-major) and cross_v bf16 [L, n_streams, H, 64, kv_ld] (positions
+ * contiguous), as written by janus_whisper_cross_kv_swapped_bf16 -- so that both contractions of the decode-time
+ * cross-attention are mma.sync tiles fed by plain 16-byte global loads (janus_b200/csrc/decoder.cu). */
+#define JANUS_DECODE_KV_SWAPPED 8
 
 typedef struct {
   int32_t batch, max_len, n_prompt;    /* max_len = n_prompt + max_new_tokens */
@@ -300,11 +305,17 @@ int32_t janus_whisper_beam_finalize(const janus_decode_state_t* state, const jan
                                     int32_t* best_tokens, float* best_score, int32_t* best_len, void* stream);
 /* One layer of decode-time cross-attention for beam search, K/V-cache form: the `beam` rows of a stream (row = stream
  * * beam + k) attend to the same K / V, which one CTA per (stream, head) streams once for all of them.
- * q / out bf16 [n_streams * beam, 64 * n_heads]; cross_k / cross_v as in janus_dec_cross_attn_bf16 with batch =
- * n_streams; 2 <= beam <= JANUS_MAX_BEAM. */
+ * q / out bf16 [n_streams * beam, 64 * n_heads]; 2 <= beam <= JANUS_MAX_BEAM. kv_layout 0: cross_k / cross_v as in
+ * janus_dec_cross_attn_bf16 with batch = n_streams (packed-FMA kernel); kv_layout 1: the JANUS_DECODE_KV_SWAPPED
+ * layouts, cross_k [n_streams, n_heads, n_ctx, 64] and cross_v [n_streams, n_heads, 64, kv_ld] (tensor-core kernel;
+ * kv_ld % 32 == 0; beam >= 1). */
 int32_t janus_dec_cross_attn_beam_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
                                        int32_t n_streams, int32_t beam, int32_t n_heads, int32_t n_ctx, int32_t kv_ld,
-                                       void* stream);
+                                       int32_t kv_layout, void* stream);
+/* janus_whisper_cross_kv_bf16 writing the JANUS_DECODE_KV_SWAPPED layouts. */
+int32_t janus_whisper_cross_kv_swapped_bf16(const janus_whisper_dims_t* dims, const janus_decoder_weights_t* weights,
+                                            const void* enc_out, int32_t batch, void* cross_k, void* cross_v,
+                                            void* stream);
 /* janus_dec_xlat_bf16 for rows that share encoder states in groups (beam search): qlat [n_rows, 16, d],
  * enc [n_rows / group, n_ctx, d], z [n_rows, n_heads, d]. */
 int32_t janus_dec_xlat_grouped_bf16(const void* qlat, const void* enc, void* z, int32_t n_rows, int32_t group,

@@ -45,7 +45,8 @@ SIGNATURES = {
     "janus_whisper_decode_step": (_I32, [_P, _P, _P, _P]),
     "janus_whisper_decode_beam_step": (_I32, [_P, _P, _P, _P, _P]),
     "janus_whisper_beam_finalize": (_I32, [_P, _P, _I32, _P, _P, _P, _P]),
-    "janus_dec_cross_attn_beam_bf16": (_I32, [_P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _P]),
+    "janus_dec_cross_attn_beam_bf16": (_I32, [_P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _I32, _P]),
+    "janus_whisper_cross_kv_swapped_bf16": (_I32, [_P, _P, _P, _I32, _P, _P, _P]),
     "janus_dec_xlat_grouped_bf16": (_I32, [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _P]),
     "janus_gemm_bf16": (_I32, [_P, _I64, _I64, _P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32,
                                _P, _P, _P, _I32, _P]),

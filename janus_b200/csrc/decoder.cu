@@ -283,7 +283,10 @@ static int xa_grid(int n_items) {
 // software-pipelines the loads across the unrolled bodies). Measured at 512 streams x 12 heads x 5 beams (2.37 GB per
 // launch, scripts/gpu_xb_bench.py): scalar FMAs 3.6-3.7 TB/s; packed 4.57 (US / UV = 8 / 4) - 4.72 TB/s (16 / 8) at 96
 // registers, 3 CTAs per SM; gathering a batch of loads up front 3.2-4.3; forcing 4 / 5 CTAs per SM through
-// __launch_bounds__ 4.0 / 2.3 (spills), 2 CTAs with 140 registers 4.1; a larger shared-memory carve-out does not help.
+// __launch_bounds__ 4.0 / 2.3 (spills), 2 CTAs with 140 registers 4.1; a larger shared-memory carve-out does not help;
+// p stored as (p, p) pairs (no MOV per packed multiplier, twice the shared memory) 4.61; the same body inlined
+// from a __device__ function 3.64 (110 more register moves around the 64-bit pairs): the schedule is fragile,
+// which is why the tensor-core kernel below (kv_layout 1) is the one beam sessions use.
 template <int NQ, int US, int UV>
 __global__ void __launch_bounds__(XA_THREADS)
 dec_cross_attn_beam_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kT,
@@ -433,9 +436,171 @@ static int launch_cross_attn_beam(const __nv_bfloat16* q, const __nv_bfloat16* k
   return JANUS_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// cross-attention for beam search on the tensor cores (kv_layout 1): K row-major [n_ctx][64], V TRANSPOSED
+// [64][kv_ld] (the two cache layouts of the greedy kernel with their roles swapped, written by the same GEMM
+// epilogue). With these layouts both contractions are mma.sync.m16n8k16 whose B fragments are plain 16-byte
+// global loads -- no shared-memory staging, no bf16 -> fp32 conversions, ~4x fewer instructions per byte than
+// the FMA kernel above, which is what lets the kernel run at the HBM rate:
+//   S[beams (rows 0-7 of the M = 16 tile; rows 8-15 are zero) x 8 keys] += Q[beams x 16 dims] K^T[16 dims x 8 keys]
+//       lane (g = lane / 4, t = lane % 4) loads dims 16t .. 16t+15 of ITS key row (2 x 16 B): the contraction
+//       index is permuted identically for Q and K, so consecutive dims feed consecutive k-steps
+//   O[beams x 8 dims] += P[beams x 16 keys] V^T[16 keys x 8 dims]: lane (g, t) loads keys 8t .. 8t+7 of dim row g
+//       (16 B); the S tiles of a 32-key block are assigned to key rows such that the lane already holds P for
+//       exactly those 8 keys in its accumulator registers (column c of tile j <-> key 8 (c / 2) + 2 j + c % 2)
+// One CTA per (stream, head), 4 warps; warp w takes the 32-key blocks w, w + 4, ... with a flash-style running
+// maximum / sum, and the four partial results are merged through shared memory.
+// ------------------------------------------------------------------------------------------
+constexpr int XM_WARPS = 4;
+
+__device__ __forceinline__ void xm_mma(float (&c)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+  // rows 8-15 of A (a1, a3) are zero: at most 8 beams
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t xm_pack_bf16(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+__global__ void __launch_bounds__(XM_WARPS * 32)
+dec_cross_attn_beam_mma_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ kc,
+                               const __nv_bfloat16* __restrict__ vt, int T, int kv_ld, int d, int H, int NQ,
+                               __nv_bfloat16* out) {
+  __shared__ float sm_m[XM_WARPS][8], sm_l[XM_WARPS][8];
+  __shared__ float sm_o[XM_WARPS][8][DH];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int item = blockIdx.x;
+  const int b = item / H, h = item - b * H;
+  const long long bh = (long long)b * H + h;
+  // Q fragments (unscaled bf16 straight from memory; the 1/8 log2(e) factor is applied to the fp32 scores)
+  uint32_t qa0[4], qa2[4];
+  {
+    const uint32_t* qrow = reinterpret_cast<const uint32_t*>(q + ((long long)b * NQ + (g < NQ ? g : 0)) * d + h * DH + 16 * t);
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      qa0[s] = g < NQ ? qrow[2 * s] : 0u;       // dims 16t + 4s, +1
+      qa2[s] = g < NQ ? qrow[2 * s + 1] : 0u;   // dims 16t + 4s + 2, +3
+    }
+  }
+  const __nv_bfloat16* K = kc + bh * (long long)T * DH;
+  const __nv_bfloat16* V = vt + bh * (long long)DH * kv_ld;
+  const float sc = 0.125f * 1.4426950408889634f;
+  float o[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o[nt][i] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;
+  const int n_blk = (T + 31) >> 5;
+#pragma unroll 1
+  for (int blk = warp; blk < n_blk; blk += XM_WARPS) {
+    const int base = blk << 5;
+    // ---- loads: 8 x 16 B of K (4 key rows x 32 B) and 8 x 16 B of V^T (8 dim rows x 8 keys)
+    uint4 ku[4][2], vu[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int row = base + 8 * (g >> 1) + 2 * j + (g & 1);
+      row = row < T ? row : T - 1;   // clamped rows are masked below
+      const uint4* kp = reinterpret_cast<const uint4*>(K + (long long)row * DH + 16 * t);
+      ku[j][0] = __ldg(kp);
+      ku[j][1] = __ldg(kp + 1);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt)
+      vu[nt] = __ldg(reinterpret_cast<const uint4*>(V + (long long)(8 * nt + g) * kv_ld + base + 8 * t));
+    // ---- scores of the 32 keys: tile j, column c <-> key base + 8 (c / 2) + 2 j + c % 2
+    float c[4][4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) c[j][i] = 0.f;
+      xm_mma(c[j], qa0[0], qa2[0], ku[j][0].x, ku[j][0].y);
+      xm_mma(c[j], qa0[1], qa2[1], ku[j][0].z, ku[j][0].w);
+      xm_mma(c[j], qa0[2], qa2[2], ku[j][1].x, ku[j][1].y);
+      xm_mma(c[j], qa0[3], qa2[3], ku[j][1].z, ku[j][1].w);
+    }
+    // this lane holds, for beam row g, the keys base + 8t + 2j + i (j = 0..3, i = 0..1) in c[j][i]
+    float mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int key = base + 8 * t + 2 * j + i;
+        c[j][i] = key < T ? c[j][i] * sc : -INFINITY;
+        mx = fmaxf(mx, c[j][i]);
+      }
+    mx = fmaxf(mx, __shfl_xor_sync(FULL_MASK, mx, 1));
+    mx = fmaxf(mx, __shfl_xor_sync(FULL_MASK, mx, 2));
+    const float m_new = fmaxf(m_run, mx);   // finite: every block holds at least one valid key
+    const float alpha = exp2f(m_run - m_new);
+    m_run = m_new;
+    l_run *= alpha;
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= alpha; o[nt][1] *= alpha; }
+    uint32_t pa[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float p0 = exp2f(c[j][0] - m_new), p1 = exp2f(c[j][1] - m_new);
+      l_run += p0 + p1;
+      pa[j] = xm_pack_bf16(p0, p1);
+    }
+    if (base + 32 > T) {   // tail block: V^T columns of keys >= T are not initialised (0 x NaN must not happen)
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        uint32_t* w = reinterpret_cast<uint32_t*>(&vu[nt]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int key = base + 8 * t + 2 * e;
+          if (key >= T) w[e] = 0u; else if (key + 1 >= T) w[e] &= 0x0000ffffu;
+        }
+      }
+    }
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+      xm_mma(o[nt], pa[0], pa[1], vu[nt].x, vu[nt].y);   // keys 8t + 0..3
+      xm_mma(o[nt], pa[2], pa[3], vu[nt].z, vu[nt].w);   // keys 8t + 4..7
+    }
+  }
+  l_run += __shfl_xor_sync(FULL_MASK, l_run, 1);
+  l_run += __shfl_xor_sync(FULL_MASK, l_run, 2);
+  if (t == 0) { sm_m[warp][g] = m_run; sm_l[warp][g] = l_run; }
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt)
+    *reinterpret_cast<float2*>(&sm_o[warp][g][8 * nt + 2 * t]) = make_float2(o[nt][0], o[nt][1]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < NQ * DH; i += XM_WARPS * 32) {
+    const int r = i / DH, e = i - r * DH;
+    float M = sm_m[0][r];
+#pragma unroll
+    for (int w = 1; w < XM_WARPS; ++w) M = fmaxf(M, sm_m[w][r]);
+    float L = 0.f, acc = 0.f;
+#pragma unroll
+    for (int w = 0; w < XM_WARPS; ++w) {
+      const float f = sm_m[w][r] == -INFINITY ? 0.f : exp2f(sm_m[w][r] - M);   // a warp without blocks (T < 128)
+      L += sm_l[w][r] * f;
+      acc += sm_o[w][r][e] * f;
+    }
+    out[((long long)b * NQ + r) * d + h * DH + e] = __float2bfloat16_rn(acc / L);
+  }
+}
+
 // q / out: [n_streams * beam, d] (row = stream * beam + k); kT / v: one layer's cross K / V of n_streams streams
+// (kv_layout 1: k is row-major [T][64] and v transposed [64][kv_ld] -> tensor-core kernel)
 static int dec_cross_attn_beam(const __nv_bfloat16* q, const __nv_bfloat16* kT, const __nv_bfloat16* v, int T, int kv_ld,
-                               int d, int H, int n_streams, int beam, __nv_bfloat16* out, cudaStream_t st) {
+                               int d, int H, int n_streams, int beam, __nv_bfloat16* out, cudaStream_t st,
+                               int kv_layout = 0) {
+  if (kv_layout == 1) {
+    JANUS_CHECK_ARG(beam >= 1 && beam <= 8 && kv_ld % 32 == 0 && kv_ld >= ((T + 31) & ~31),
+                    "cross_attn_beam (mma): beam=%d / kv_ld=%d unsupported", beam, kv_ld);
+    JANUS_CUDA(launch_pdl(dec_cross_attn_beam_mma_kernel, dim3(H * n_streams), dim3(XM_WARPS * 32), 0, st, q, kT, v, T, kv_ld,
+                          d, H, beam, out));
+    return JANUS_OK;
+  }
   switch (beam) {
     case 2: return launch_cross_attn_beam<2, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
     case 3: return launch_cross_attn_beam<3, 16, 8>(q, kT, v, T, kv_ld, d, H, n_streams, out, st);
@@ -640,29 +805,42 @@ extern "C" int32_t janus_dec_cross_attn_bf16(const void* q, const void* cross_k,
 
 extern "C" int32_t janus_dec_cross_attn_beam_bf16(const void* q, const void* cross_k, const void* cross_v, void* out,
                                                   int32_t n_streams, int32_t beam, int32_t n_heads, int32_t n_ctx,
-                                                  int32_t kv_ld, void* stream) {
+                                                  int32_t kv_ld, int32_t kv_layout, void* stream) {
+  JANUS_CHECK_ARG(kv_layout == 0 || kv_layout == 1, "cross_attn_beam: kv_layout must be 0 or 1");
   JANUS_CHECK_ARG(q && cross_k && cross_v && out && n_streams > 0 && n_heads > 0, "cross_attn_beam: bad argument");
-  JANUS_CHECK_ARG(beam >= 2 && beam <= JANUS_MAX_BEAM, "cross_attn_beam: beam=%d must be in 2 .. %d", beam, JANUS_MAX_BEAM);
+  JANUS_CHECK_ARG(beam >= (kv_layout ? 1 : 2) && beam <= JANUS_MAX_BEAM, "cross_attn_beam: beam=%d must be in %d .. %d", beam,
+                  kv_layout ? 1 : 2, JANUS_MAX_BEAM);
   JANUS_CHECK_ARG(n_ctx <= XA_THREADS * 8 && kv_ld % 8 == 0 && kv_ld >= n_ctx && kv_ld <= XA_THREADS * 8,
                   "cross_attn_beam: n_ctx=%d / kv_ld=%d unsupported", n_ctx, kv_ld);
   return dec_cross_attn_beam(static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(cross_k),
                              static_cast<const __nv_bfloat16*>(cross_v), n_ctx, kv_ld, n_heads * DH, n_heads, n_streams,
-                             beam, static_cast<__nv_bfloat16*>(out), (cudaStream_t)stream);
+                             beam, static_cast<__nv_bfloat16*>(out), (cudaStream_t)stream, kv_layout);
 }
 
-extern "C" int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
-                                               const void* enc_out, int32_t batch, void* cross_k, void* cross_v,
-                                               void* stream) {
+static int32_t cross_kv_impl(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w, const void* enc_out,
+                             int32_t batch, void* cross_k, void* cross_v, int kv_swap, void* stream) {
   JANUS_CHECK_ARG(c && w && enc_out && cross_k && cross_v && batch > 0, "cross_kv: bad argument");
   const int T = c->n_ctx, d = c->d;
   GemmParams p = {};
   p.M_per_batch = T; p.n_batch = batch; p.N = c->n_layers * 2 * d; p.K = d;
   p.bias = w->b_ckv; p.store_mode = STORE_CROSS_KV;
   p.kv_k = static_cast<__nv_bfloat16*>(cross_k); p.kv_v = static_cast<__nv_bfloat16*>(cross_v);
-  p.kv_d = d; p.kv_heads = c->n_heads; p.kv_ld = w->kv_ld;
+  p.kv_d = d; p.kv_heads = c->n_heads; p.kv_ld = w->kv_ld; p.kv_swap = kv_swap;
   p.ldc = 0; p.out_batch_stride = 0;
   return gemm_bf16(static_cast<const __nv_bfloat16*>(enc_out), d, (long long)T * d,
                    static_cast<const __nv_bfloat16*>(w->w_ckv), d, p, (cudaStream_t)stream);
+}
+
+extern "C" int32_t janus_whisper_cross_kv_bf16(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                               const void* enc_out, int32_t batch, void* cross_k, void* cross_v,
+                                               void* stream) {
+  return cross_kv_impl(c, w, enc_out, batch, cross_k, cross_v, 0, stream);
+}
+
+extern "C" int32_t janus_whisper_cross_kv_swapped_bf16(const janus_whisper_dims_t* c, const janus_decoder_weights_t* w,
+                                                       const void* enc_out, int32_t batch, void* cross_k, void* cross_v,
+                                                       void* stream) {
+  return cross_kv_impl(c, w, enc_out, batch, cross_k, cross_v, 1, stream);
 }
 
 // One decode step for s->batch rows. bm == nullptr: greedy (a row is a stream). bm != nullptr: beam search, rows are
@@ -702,8 +880,12 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
   JANUS_CHECK_ARG(self_ld >= s->max_len && self_ld <= 512, "decode_step: self_ld=%d must be in [max_len=%d, 512]", self_ld,
                   s->max_len);
   const long long self_stride = (long long)B * H * self_ld * DH;
-  const long long ck_stride = (long long)(B / grp) * H * DH * w->kv_ld;   // cross K/V exist once per stream
-  const long long cv_stride = (long long)(B / grp) * H * T * DH;
+  const bool kv_swapped = (s->flags & JANUS_DECODE_KV_SWAPPED) != 0;
+  JANUS_CHECK_ARG(!kv_swapped || (bm && !latent), "decode_step: JANUS_DECODE_KV_SWAPPED is a beam-search K/V layout");
+  const long long kt_stride = (long long)(B / grp) * H * DH * w->kv_ld;   // cross K/V exist once per stream
+  const long long rm_stride = (long long)(B / grp) * H * T * DH;
+  const long long ck_stride = kv_swapped ? rm_stride : kt_stride;
+  const long long cv_stride = kv_swapped ? kt_stride : rm_stride;
   if (fused) {
     FusedProgram base = {};
     base.rows = B; base.d = d; base.n_heads = H; base.pos = s->pos;
@@ -792,10 +974,10 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
         if ((rc = gemm_bf16(zlat, (long long)H * d, d, static_cast<const __nv_bfloat16*>(L.w_cv), d, g, st))) return rc;
       }
     } else {
-    if (grp > 1) {   // beam search: one CTA per (stream, head) serves all beams from one pass over K / V
+    if (grp > 1 || kv_swapped) {   // beam search: one CTA per (stream, head) serves all beams from one pass over K / V
       if ((rc = dec_cross_attn_beam(q, static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
                                     static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H,
-                                    B / grp, grp, att, st))) return rc;
+                                    B / grp, grp, att, st, kv_swapped ? 1 : 0))) return rc;
     } else {
     JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
                           static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,

@@ -352,8 +352,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const int f0 = rem - is_v * p.kv_d;
             const int h = f0 >> 6, dim0 = f0 & 63;
             const long long bh = ((long long)l * p.n_batch + b) * p.kv_heads + h;
-            if (is_v) {
-              uint4* op = reinterpret_cast<uint4*>(p.kv_v + (bh * p.M_per_batch + t) * 64 + dim0);
+            __nv_bfloat16* base = is_v ? p.kv_v : p.kv_k;
+            if (is_v != p.kv_swap) {   // row-major [t][64] (V by default, K with kv_swap)
+              uint4* op = reinterpret_cast<uint4*>(base + (bh * p.M_per_batch + t) * 64 + dim0);
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 uint4 u;
@@ -362,8 +363,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 for (int j = 0; j < 4; ++j) hh[j] = __floats2bfloat162_rn(v[i * 8 + 2 * j], v[i * 8 + 2 * j + 1]);
                 op[i] = u;
               }
-            } else {
-              __nv_bfloat16* op = p.kv_k + (bh * 64 + dim0) * p.kv_ld + t;
+            } else {                   // transposed [64][kv_ld], positions contiguous (K by default, V with kv_swap)
+              __nv_bfloat16* op = base + (bh * 64 + dim0) * p.kv_ld + t;
 #pragma unroll
               for (int i = 0; i < 32; ++i) op[(long long)i * p.kv_ld] = __float2bfloat16_rn(v[i]);
             }

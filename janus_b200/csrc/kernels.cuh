@@ -23,6 +23,7 @@ struct GemmParams {
   __nv_bfloat16* kv_k;
   __nv_bfloat16* kv_v;
   int kv_d, kv_heads, kv_ld;
+  int kv_swap;  // 1: the two layouts swap roles -- K row-major k[l][b][h][t][64], V transposed v[l][b][h][64][kv_ld]
   int bn_max;  // 0 = auto; otherwise cap the N tile (skinny-M decode GEMMs want many small tiles)
   // grouped GEMM: batch b multiplies by W rows [b * w_batch_rows, b * w_batch_rows + N) and adds
   // bias[b * bias_batch_stride + n]; 0 = every batch shares W / bias

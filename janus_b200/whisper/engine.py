@@ -200,6 +200,7 @@ class DecodeSession:
     DECODE_LIGHT = 1   # JANUS_DECODE_LIGHT
     DECODE_FUSED = 2   # JANUS_DECODE_FUSED
     DECODE_LATENT = 4  # JANUS_DECODE_LATENT
+    DECODE_KV_SWAPPED = 8  # JANUS_DECODE_KV_SWAPPED
     LATENT_MIN_BATCH = 128   # the latent kernel runs one CTA per window: below ~one window per SM the K/V kernel
                              # (one CTA per window and head) fills the machine better
 
@@ -250,6 +251,11 @@ class DecodeSession:
             self.enc_buf = torch.zeros((NW, d.n_audio_ctx, n), **bf)
             self.qlat = torch.zeros((B, 16, n), **bf)      # rows >= H stay zero
             self.zlat = torch.zeros((B, H, n), **bf)
+        elif beam:
+            # beam search, K/V form: K row-major / V transposed, the layouts of the tensor-core kernel
+            # (dec_cross_attn_beam_mma_kernel) that serves all beams of a window from one pass over K / V
+            self.cross_k = torch.zeros((L, NW, H, d.n_audio_ctx, 64), **bf)
+            self.cross_v = torch.zeros((L, NW, H, 64, engine.kv_ld), **bf)
         else:
             self.cross_k = torch.zeros((L, NW, H, 64, engine.kv_ld), **bf)
             self.cross_v = torch.zeros((L, NW, H, d.n_audio_ctx, 64), **bf)
@@ -264,7 +270,7 @@ class DecodeSession:
         if light and B > 64:
             raise ValueError("light decode sessions hold at most 64 streams")
         s.flags = (self.DECODE_LIGHT if light else 0) | (self.DECODE_FUSED if fused else 0) | \
-                  (self.DECODE_LATENT if latent else 0)
+                  (self.DECODE_LATENT if latent else 0) | (self.DECODE_KV_SWAPPED if beam and not latent else 0)
         self.barrier = torch.zeros(2, dtype=torch.int64, device=dev)   # grid-barrier counter of the fused path
         s.barrier = self.barrier.data_ptr()
         self.fused = fused
@@ -367,8 +373,8 @@ class DecodeSession:
             if enc_out.data_ptr() != self.enc_buf.data_ptr():
                 self.enc_buf.copy_(enc_out)
             return
-        _abi.call("janus_whisper_cross_kv_bf16", C.byref(e.c_dec_dims), C.byref(e.dec_weights), enc_out.data_ptr(),
-                  self.n_windows, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
+        _abi.call("janus_whisper_cross_kv_swapped_bf16" if self.beam else "janus_whisper_cross_kv_bf16",
+                  C.byref(e.c_dec_dims), C.byref(e.dec_weights), enc_out.data_ptr(), self.n_windows, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
                   torch.cuda.current_stream(e.device).cuda_stream)
 
     def _ensure_graph(self) -> None:

@@ -20,14 +20,19 @@ def main():
     rows = n * beam
     q = torch.randn(rows, d, device="cuda").bfloat16()
     L = 4   # distinct layers so that consecutive launches do not hit L2
-    kT = torch.randn(L, n, H, 64, kv_ld, device="cuda").bfloat16()
-    v = torch.randn(L, n, H, T, 64, device="cuda").bfloat16()
+    layout = int(os.environ.get("KV_LAYOUT", "1"))   # 1: K row-major / V transposed (tensor-core kernel)
+    if layout:
+        kT = torch.randn(L, n, H, T, 64, device="cuda").bfloat16()
+        v = torch.randn(L, n, H, 64, kv_ld, device="cuda").bfloat16()
+    else:
+        kT = torch.randn(L, n, H, 64, kv_ld, device="cuda").bfloat16()
+        v = torch.randn(L, n, H, T, 64, device="cuda").bfloat16()
     out = torch.empty(rows, d, device="cuda", dtype=torch.bfloat16)
     st = torch.cuda.current_stream()
 
     def run(l):
         _abi.call("janus_dec_cross_attn_beam_bf16", q.data_ptr(), kT[l].data_ptr(), v[l].data_ptr(), out.data_ptr(), n,
-                  beam, H, T, kv_ld, st.cuda_stream)
+                  beam, H, T, kv_ld, layout, st.cuda_stream)
 
     for l in range(L):
         run(l)
@@ -42,7 +47,7 @@ def main():
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / (reps * L)
     alg = n * H * 2 * T * 64 * 2 + 2 * rows * d * 2
-    print(f"variant={os.environ.get('JANUS_XB_VARIANT', '0')} n_streams={n} H={H} beam={beam}: {ms:.4f} ms per launch, "
+    print(f"kv_layout={layout} n_streams={n} H={H} beam={beam}: {ms:.4f} ms per launch, "
           f"{alg / ms / 1e6:.0f} GB/s algorithmic")
 
 

@@ -2,7 +2,7 @@
 vs the fp32 CPU oracle's beam_decode (oracle/whisper_ref.py).
 
 Stated bars:
-  * beam = 1 is the greedy decoder: tokens bit-identical to the greedy session of the same engine;
+  * beam = 1 is the greedy decoder: tokens identical to the greedy session of the same engine;
   * "confident" weights (margins >> bf16 noise): the best hypothesis of every window equals the oracle's wherever
     the oracle's best / second-best normalised scores differ by more than SCORE_MARGIN, its sum of log-probs is
     within LP_TOL, and the list of finished hypotheses (tokens, order, lengths) equals the oracle's wherever the
@@ -60,7 +60,9 @@ def test_beam1_is_greedy(latent):
     bt, blp = b.decode(enc)
     torch.cuda.synchronize()
     assert torch.equal(gt.cpu(), bt.cpu())
-    assert torch.allclose(glp.cpu(), blp.cpu(), atol=1e-3)
+    # latent: the same kernels run in both sessions; K/V form: the beam session's cross-attention is the tensor-core
+    # kernel (p rounded to bf16 for the second MMA), the greedy session's the fp32 FMA kernel
+    assert torch.allclose(glp.cpu(), blp.cpu(), atol=1e-3 if latent else LP_TOL)
 
 
 def _norm(score, length):
@@ -115,10 +117,13 @@ def test_beam5_vs_oracle(latent, eot_scale, use_graph, d, heads):
             assert [int(n >= K) for n in n_fin] == done
 
 
-@pytest.mark.parametrize("n_streams,beam,T,H", [(3, 5, 1500, 12), (9, 2, 700, 6), (4, 8, 1500, 20), (40, 5, 333, 12)])
-def test_cross_attn_beam_kernel_equals_per_row_kernel(n_streams, beam, T, H):
-    """The K/V cross-attention that serves all beams of a stream from one pass over K / V against the greedy kernel
-    on replicated K / V (same arithmetic per query: bf16-ulp bar)."""
+@pytest.mark.parametrize("layout", [0, 1])
+@pytest.mark.parametrize("n_streams,beam,T,H", [(3, 5, 1500, 12), (9, 2, 700, 6), (4, 8, 1500, 20), (40, 5, 333, 12),
+                                                (2, 3, 70, 2)])
+def test_cross_attn_beam_kernel_equals_per_row_kernel(n_streams, beam, T, H, layout):
+    """The K/V cross-attention kernels that serve all beams of a stream from one pass over K / V (layout 0: packed
+    FMAs on the greedy layouts; layout 1: mma.sync on K row-major / V transposed) against the greedy kernel on
+    replicated K / V. Bar: 4e-3 of the output scale (layout 1 rounds p to bf16 for the second MMA)."""
     from janus_b200 import _abi
     g = torch.Generator(device="cuda").manual_seed(5)
     d, kv_ld = 64 * H, -(-T // 64) * 64
@@ -129,13 +134,20 @@ def test_cross_attn_beam_kernel_equals_per_row_kernel(n_streams, beam, T, H):
     o1 = torch.full((rows, d), float("nan"), device="cuda", dtype=torch.bfloat16)
     o2 = torch.full((rows, d), float("nan"), device="cuda", dtype=torch.bfloat16)
     st = torch.cuda.current_stream().cuda_stream
-    _abi.call("janus_dec_cross_attn_beam_bf16", q.data_ptr(), kT.data_ptr(), v.data_ptr(), o1.data_ptr(), n_streams, beam,
-              H, T, kv_ld, st)
+    if layout == 1:
+        k_in = kT[..., :T].transpose(-1, -2).contiguous()                      # [n, H, T, 64]
+        v_in = torch.full((n_streams, H, 64, kv_ld), float("nan"), device="cuda", dtype=torch.bfloat16)
+        v_in[..., :T] = v.transpose(-1, -2)                                     # pad keys stay NaN: must be masked
+    else:
+        k_in, v_in = kT, v
+    _abi.call("janus_dec_cross_attn_beam_bf16", q.data_ptr(), k_in.data_ptr(), v_in.data_ptr(), o1.data_ptr(), n_streams,
+              beam, H, T, kv_ld, layout, st)
     kr, vr = kT.repeat_interleave(beam, 0).contiguous(), v.repeat_interleave(beam, 0).contiguous()
     _abi.call("janus_dec_cross_attn_bf16", q.data_ptr(), kr.data_ptr(), vr.data_ptr(), o2.data_ptr(), rows, H, T, kv_ld, st)
     torch.cuda.synchronize()
     assert torch.isfinite(o1.float()).all()
-    assert (o1.float() - o2.float()).abs().max().item() <= 2e-3 * max(1.0, o2.float().abs().max().item())
+    err = (o1.float() - o2.float()).abs().max().item()
+    assert err <= 4e-3 * max(1.0, o2.float().abs().max().item()), err
 
 
 @pytest.mark.parametrize("n_streams,group,T,d,H", [(7, 5, 1500, 768, 12), (40, 5, 300, 768, 12), (6, 4, 200, 384, 6),
