@@ -25,60 +25,69 @@ namespace janus {
 constexpr int BC_THREADS = 512;
 constexpr int BC_KC = JANUS_MAX_BEAM + 1;   // candidates per row, compile-time bound
 
-struct RuleState {   // ApplyTimestampRules / SuppressBlank state of one row (same rules as dec_pick_kernel)
-  int n_gen, tb, ts_floor, first_hi, eot, blank;
-  bool last_ts, penult_ts;
+struct RuleState {   // SuppressBlank / ApplyTimestampRules of one row (the rules of dec_pick_kernel) as two index ranges:
+  int t_lo, t_hi;    // allowed text tokens   [t_lo, t_hi)  within [0, timestamp_begin)
+  int s_lo, s_hi;    // allowed timestamps    [s_lo, s_hi)  within [timestamp_begin, n_vocab)
 };
 
 __device__ __forceinline__ RuleState rule_state(const int32_t* toks, int nxt, int n_prompt, int tb, int max_initial_ts,
-                                                int eot, int blank) {
-  RuleState r;
-  r.n_gen = nxt - n_prompt;
-  r.tb = tb;
-  r.eot = eot;
-  r.blank = blank;
-  const int last = r.n_gen >= 1 ? toks[nxt - 1] : -1;
-  const int penult = r.n_gen >= 2 ? toks[nxt - 2] : -1;
-  r.last_ts = r.n_gen >= 1 && last >= tb;
-  r.penult_ts = r.n_gen < 2 || penult >= tb;
-  r.ts_floor = tb;
-  int last_stamp = -1;
+                                                int eot, int n_vocab) {
+  const int n_gen = nxt - n_prompt;
+  const int last = n_gen >= 1 ? toks[nxt - 1] : -1;
+  const int penult = n_gen >= 2 ? toks[nxt - 2] : -1;
+  const bool last_ts = n_gen >= 1 && last >= tb;
+  const bool penult_ts = n_gen < 2 || penult >= tb;
+  int ts_floor = tb, last_stamp = -1;   // timestamps never decrease
   for (int i = n_prompt; i < nxt; ++i) {
     const int t = toks[i];
     if (t >= tb) last_stamp = t;
   }
-  if (last_stamp >= 0) r.ts_floor = (r.last_ts && !r.penult_ts) ? last_stamp : last_stamp + 1;
-  r.first_hi = tb + max_initial_ts;
+  if (last_stamp >= 0) ts_floor = (last_ts && !penult_ts) ? last_stamp : last_stamp + 1;
+  RuleState r;
+  r.t_lo = 0; r.t_hi = tb; r.s_lo = ts_floor; r.s_hi = n_vocab;
+  if (n_gen == 0) {            // first sampled token: a timestamp no later than max_initial_timestamp (blank, eot < tb)
+    r.t_hi = 0;
+    r.s_lo = tb;
+    r.s_hi = tb + max_initial_ts + 1;
+  }
+  if (last_ts) {               // timestamps come in pairs
+    if (penult_ts) r.s_hi = r.s_lo;   // ... <ts><ts>: text only
+    else r.t_lo = eot;                // ... <text><ts>: a timestamp or eot-and-above, no normal text
+  }
+  if (r.s_hi < r.s_lo) r.s_hi = r.s_lo;
+  if (r.t_hi < r.t_lo) r.t_hi = r.t_lo;
   return r;
 }
 
 __device__ __forceinline__ bool rule_allows(const RuleState& r, int i, bool suppressed) {
-  bool ok = !suppressed;
-  if (r.n_gen == 0) ok = ok && i != r.blank && i != r.eot && i >= r.tb && i <= r.first_hi;
-  if (r.last_ts) ok = ok && (r.penult_ts ? i < r.tb : i >= r.eot);
-  if (i >= r.tb) ok = ok && i >= r.ts_floor;
-  return ok;
+  return !suppressed && ((unsigned)(i - r.t_lo) < (unsigned)(r.t_hi - r.t_lo) || (unsigned)(i - r.s_lo) < (unsigned)(r.s_hi - r.s_lo));
 }
 
-struct MaxSum {   // running max and sum exp(x - max)
-  float m, s;
+struct MaxSum {   // running max m and sum 2^(y - m) of y = logit * log2(e); m starts at a large negative FINITE value so
+  float m, s;     // that masked tokens (y = -inf) and the first token need no branch (2^(-inf) = 0, no inf - inf)
 };
-__device__ __forceinline__ void ms_add(MaxSum& a, float x) {
-  if (x > a.m) {
-    a.s = a.s * __expf(a.m - x) + 1.f;
-    a.m = x;
-  } else {
-    a.s += __expf(x - a.m);
+constexpr float MS_EMPTY = -1e30f;
+__device__ __forceinline__ float ms_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void ms_add4(MaxSum& a, float y0, float y1, float y2, float y3) {
+  const float m4 = fmaxf(fmaxf(y0, y1), fmaxf(y2, y3));
+  if (m4 > a.m) {   // rare after the first few tokens
+    a.s *= ms_ex2(a.m - m4);
+    a.m = m4;
   }
+  a.s += (ms_ex2(y0 - a.m) + ms_ex2(y1 - a.m)) + (ms_ex2(y2 - a.m) + ms_ex2(y3 - a.m));
 }
 __device__ __forceinline__ void ms_merge(MaxSum& a, float om, float os) {
-  if (om == -INFINITY) return;
-  if (a.m == -INFINITY) { a.m = om; a.s = os; return; }
+  if (os == 0.f) return;
+  if (a.s == 0.f) { a.m = om; a.s = os; return; }
   if (om > a.m) {
-    a.s = a.s * __expf(a.m - om) + os;
+    a.s = a.s * ms_ex2(a.m - om) + os;
     a.m = om;
   } else {
-    a.s += os * __expf(om - a.m);
+    a.s += os * ms_ex2(om - a.m);
   }
 }
 
@@ -93,14 +102,64 @@ __device__ __forceinline__ uint32_t load_suppress4(const uint8_t* sup, int i0, i
 __device__ __forceinline__ bool cand_before(float v, int i, float bv, int bi) { return v > bv || (v == bv && i < bi); }
 
 // ------------------------------------------------------------------------------------------
-// candidates: one CTA per row. Pass 1: max / sum-exp of the allowed text and timestamp tokens (decides the
-// "timestamps outweigh every text token" rule and the normaliser). Pass 2 (the row is L2 / L1 resident): every
-// thread keeps the top kc of its tokens in registers; kc rounds of a block arg-max merge them.
+// candidates: one CTA per row, ONE pass over the 209 KB of fp32 logits. Every thread keeps max / sum-exp of its
+// allowed text and timestamp tokens; the top-kc lists are kept PER WARP in shared memory, guarded by a warp-uniform
+// threshold (the list's current kc-th entry): a token enters the insertion path only if it beats the threshold,
+// which after the first few hundred tokens almost never happens (~kc ln(n / kc) insertions per list), so the scan
+// stays convergent. (Per-thread register lists made every warp run the 9-slot insertion code on nearly every
+// token -- some lane always had an insertion -- and cost 0.9-1.1 ms per step at 2560 rows.) Two lists per warp --
+// all allowed tokens / timestamps only -- because the "timestamps outweigh every text token" rule, which decides
+// whether text is masked and which normaliser applies, is only known after the block reduction.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BC_THREADS) dec_beam_cand_kernel(const BeamStepParams p) {
-  __shared__ float sh_m[2][BC_THREADS / 32], sh_s[2][BC_THREADS / 32];
-  __shared__ float win_v[2][BC_THREADS / 32];
-  __shared__ int win_i[2][BC_THREADS / 32];
+constexpr int BC_WARPS = BC_THREADS / 32;
+
+struct WarpList {   // sorted by (value desc, index asc)
+  float v[BC_KC];
+  int i[BC_KC];
+};
+
+// lanes with `pred` insert (x, idx) into the warp's list one after the other; returns with thr = the kc-th entry
+__device__ __forceinline__ void warp_list_offer(WarpList& wl, int kc, bool pred, float x, int idx, float& thr_v,
+                                                int& thr_i, int lane) {
+  unsigned pending = __ballot_sync(FULL_MASK, pred);
+  while (pending) {
+    const int src = __ffs(pending) - 1;
+    if (lane == src) {
+      int j = kc - 1;   // shift entries that come after (x, idx) down by one
+      while (j > 0 && cand_before(x, idx, wl.v[j - 1], wl.i[j - 1])) {
+        wl.v[j] = wl.v[j - 1];
+        wl.i[j] = wl.i[j - 1];
+        --j;
+      }
+      wl.v[j] = x;
+      wl.i[j] = idx;
+    }
+    __syncwarp();
+    thr_v = wl.v[kc - 1];
+    thr_i = wl.i[kc - 1];
+    pending &= pending - 1;
+    // a lane whose token no longer beats the raised threshold drops out
+    pending &= __ballot_sync(FULL_MASK, pred && cand_before(x, idx, thr_v, thr_i));
+    __syncwarp();
+  }
+}
+
+// order-preserving float <-> int map (for atomicMax on the block-wide thresholds)
+__device__ __forceinline__ int f2ord(float f) {
+  int k = __float_as_int(f);
+  return k ^ ((k >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float ord2f(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
+
+__global__ void __launch_bounds__(BC_THREADS, 3) dec_beam_cand_kernel(const BeamStepParams p) {
+  __shared__ float sh_m[2][BC_WARPS], sh_s[2][BC_WARPS];
+  // block-wide value thresholds: the largest kc-th entry any warp holds. kc tokens >= it exist in the row, so a token
+  // below it can never be among the row's top kc -- with it a warp enters the insertion path ~once per row instead
+  // of once per iteration (a warp alone sees only 1/16 of the row and its own threshold rises slowly)
+  __shared__ int thr_blk[2];
+  __shared__ int sh_wmax[BC_WARPS];
+  __shared__ WarpList lists[2][BC_WARPS];   // [all allowed | timestamps only][warp]
+  __shared__ RuleState sh_rs;
   const int row = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   pdl_launch_dependents();
   pdl_wait();
@@ -108,21 +167,123 @@ __global__ void __launch_bounds__(BC_THREADS) dec_beam_cand_kernel(const BeamSte
   if (nxt >= p.max_len || nxt < p.n_prompt) return;
   const int K = p.bm.beam, kc = K + 1;
   if (p.bm.stream_done[row / K]) return;
-  const int32_t* toks = p.tokens + (long long)row * p.max_len;
-  const RuleState rs = rule_state(toks, nxt, p.n_prompt, p.ts_begin, p.max_initial_ts, p.eot, p.blank);
+  if (tid == 0)
+    sh_rs = rule_state(p.tokens + (long long)row * p.max_len, nxt, p.n_prompt, p.ts_begin, p.max_initial_ts, p.eot, p.n_vocab);
+  if (tid < 2) thr_blk[tid] = f2ord(-INFINITY);
+  if (lane < BC_KC) {
+    lists[0][wid].v[lane] = lists[1][wid].v[lane] = -INFINITY;
+    lists[0][wid].i[lane] = lists[1][wid].i[lane] = 0x7fffffff;
+  }
+  __syncthreads();
+  const RuleState rs = sh_rs;
   const float* lg = p.logits + (long long)row * p.n_vocab_pad;
   const int tb = p.ts_begin;
-  // ---- pass 1
-  MaxSum text = {-INFINITY, 0.f}, ts = {-INFINITY, 0.f};
-  for (int i0 = tid * 4; i0 < p.n_vocab; i0 += BC_THREADS * 4) {
-    const float4 x4 = *reinterpret_cast<const float4*>(lg + i0);
-    const uint32_t sup4 = load_suppress4(p.suppress, i0, p.n_vocab);
-    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+  {
+    // Warm start of the block-wide threshold: the kc-th largest of the 16 warps' maxima over the row's first 4096
+    // tokens. Those maxima are 16 different allowed tokens, so kc tokens >= it exist. Without it every warp fills
+    // its list by ~50 serial insertions (60 % of the kernel's instructions); with it ~5.
+    int best = f2ord(-INFINITY);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int i = i0 + e;
-      if (!rule_allows(rs, i, ((sup4 >> (8 * e)) & 0xffu) != 0)) continue;
-      if (i < tb) ms_add(text, xs[e]); else ms_add(ts, xs[e]);
+    for (int h = 0; h < 2; ++h) {
+      const int i0 = tid * 4 + h * BC_THREADS * 4;
+      if (i0 < p.n_vocab) {
+        const float4 x4 = *reinterpret_cast<const float4*>(lg + i0);
+        const uint32_t s4 = load_suppress4(p.suppress, i0, p.n_vocab);
+        const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (i0 + e < p.n_vocab && rule_allows(rs, i0 + e, ((s4 >> (8 * e)) & 0xffu) != 0)) best = max(best, f2ord(xs[e]));
+      }
+    }
+    best = __reduce_max_sync(FULL_MASK, best);
+    if (lane == 0) sh_wmax[wid] = best;
+    __syncthreads();
+    if (tid == 0) {
+      int v[BC_WARPS];
+      for (int w = 0; w < BC_WARPS; ++w) v[w] = sh_wmax[w];
+      for (int r = 0; r < kc; ++r) {   // selection of the kc largest (kc <= 9 <= 16 warps)
+        int b = r;
+        for (int w = r + 1; w < BC_WARPS; ++w) if (v[w] > v[b]) b = w;
+        const int t_ = v[r]; v[r] = v[b]; v[b] = t_;
+      }
+      thr_blk[0] = v[kc - 1];   // -inf if fewer than kc warps saw an allowed token
+    }
+    __syncthreads();
+  }
+  MaxSum text = {MS_EMPTY, 0.f}, ts = {MS_EMPTY, 0.f};
+  float thr_av = -INFINITY, thr_tv = -INFINITY;
+  int thr_ai = 0x7fffffff, thr_ti = 0x7fffffff;
+  WarpList& la = lists[0][wid];
+  WarpList& lt = lists[1][wid];
+  constexpr int STEP = BC_THREADS * 4;
+  constexpr float LOG2E = 1.4426950408889634f;
+  for (int i0 = tid * 4; i0 - tid * 4 < p.n_vocab; i0 += 2 * STEP) {   // warp-uniform trip count (votes inside)
+    // n_vocab_pad is a multiple of 256 and rows are zero-padded: a load that starts below n_vocab never leaves the row
+    const int i1 = i0 + STEP;
+    const bool has0 = i0 < p.n_vocab, has1 = i1 < p.n_vocab;
+    const float4 xa = has0 ? *reinterpret_cast<const float4*>(lg + i0) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 xb = has1 ? *reinterpret_cast<const float4*>(lg + i1) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const uint32_t sa = has0 ? load_suppress4(p.suppress, i0, p.n_vocab) : 0x01010101u;
+    const uint32_t sb = has1 ? load_suppress4(p.suppress, i1, p.n_vocab) : 0x01010101u;
+    const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    // fast path (branch-free per token): range filter, statistics per group of 4, and ONE vote per list on whether
+    // any of the 8 tokens reaches the threshold max(block-wide, this warp's); the insertion path runs only then
+    const float gate_a = fmaxf(ord2f(*reinterpret_cast<volatile int*>(&thr_blk[0])), thr_av);
+    const float gate_t = fmaxf(ord2f(*reinterpret_cast<volatile int*>(&thr_blk[1])), thr_tv);
+    unsigned okm = 0;
+    float y[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int i = (e < 4 ? i0 : i1) + (e & 3);
+      const uint32_t sup = ((e < 4 ? sa : sb) >> (8 * (e & 3))) & 0xffu;
+      const bool ok = i < p.n_vocab && rule_allows(rs, i, sup != 0);
+      okm |= (unsigned)ok << e;
+      y[e] = ok ? xs[e] * LOG2E : -INFINITY;
+    }
+    unsigned hit_a = 0, hit_t = 0;
+#pragma unroll
+    for (int g4 = 0; g4 < 2; ++g4) {
+      const int ib = g4 ? i1 : i0;
+      const float* yy = y + 4 * g4;
+      unsigned tsm;   // which of the group's 4 tokens are timestamps
+      if (ib + 3 < tb) {
+        ms_add4(text, yy[0], yy[1], yy[2], yy[3]);
+        tsm = 0;
+      } else if (ib >= tb) {
+        ms_add4(ts, yy[0], yy[1], yy[2], yy[3]);
+        tsm = 0xf;
+      } else {   // the one group of the row that straddles timestamp_begin
+        tsm = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) tsm |= (unsigned)(ib + e >= tb) << e;
+        ms_add4(text, (tsm & 1) ? -INFINITY : yy[0], (tsm & 2) ? -INFINITY : yy[1], (tsm & 4) ? -INFINITY : yy[2],
+                (tsm & 8) ? -INFINITY : yy[3]);
+        ms_add4(ts, (tsm & 1) ? yy[0] : -INFINITY, (tsm & 2) ? yy[1] : -INFINITY, (tsm & 4) ? yy[2] : -INFINITY,
+                (tsm & 8) ? yy[3] : -INFINITY);
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const unsigned ok = (okm >> (4 * g4 + e)) & 1u;
+        const float x = xs[4 * g4 + e];
+        hit_a |= (ok & (unsigned)(x >= gate_a)) << (4 * g4 + e);
+        hit_t |= (ok & ((tsm >> e) & 1u) & (unsigned)(x >= gate_t)) << (4 * g4 + e);
+      }
+    }
+    if (__any_sync(FULL_MASK, hit_a != 0)) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int i = (e < 4 ? i0 : i1) + (e & 3);
+        warp_list_offer(la, kc, ((hit_a >> e) & 1u) && cand_before(xs[e], i, thr_av, thr_ai), xs[e], i, thr_av, thr_ai, lane);
+      }
+      if (lane == 0) atomicMax(&thr_blk[0], f2ord(thr_av));
+    }
+    if (__any_sync(FULL_MASK, hit_t != 0)) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int i = (e < 4 ? i0 : i1) + (e & 3);
+        warp_list_offer(lt, kc, ((hit_t >> e) & 1u) && cand_before(xs[e], i, thr_tv, thr_ti), xs[e], i, thr_tv, thr_ti, lane);
+      }
+      if (lane == 0) atomicMax(&thr_blk[1], f2ord(thr_tv));
     }
   }
 #pragma unroll
@@ -133,67 +294,51 @@ __global__ void __launch_bounds__(BC_THREADS) dec_beam_cand_kernel(const BeamSte
   if (lane == 0) { sh_m[0][wid] = text.m; sh_s[0][wid] = text.s; sh_m[1][wid] = ts.m; sh_s[1][wid] = ts.s; }
   __syncthreads();
   text.m = sh_m[0][0]; text.s = sh_s[0][0]; ts.m = sh_m[1][0]; ts.s = sh_s[1][0];
-  for (int w = 1; w < BC_THREADS / 32; ++w) { ms_merge(text, sh_m[0][w], sh_s[0][w]); ms_merge(ts, sh_m[1][w], sh_s[1][w]); }
-  const float lse_ts = ts.m == -INFINITY ? -INFINITY : ts.m + logf(ts.s);
-  const bool ts_only = lse_ts > text.m;   // timestamps carry more mass than any text token: text is masked
+  for (int w = 1; w < BC_WARPS; ++w) { ms_merge(text, sh_m[0][w], sh_s[0][w]); ms_merge(ts, sh_m[1][w], sh_s[1][w]); }
+  // back to natural-log units: max text logit, log-sum-exp of the timestamps / of everything allowed
+  const float text_max = text.s == 0.f ? -INFINITY : text.m / LOG2E;
+  const float lse_ts = ts.s == 0.f ? -INFINITY : (ts.m + log2f(ts.s)) / LOG2E;
+  const bool ts_only = lse_ts > text_max;   // timestamps carry more mass than any text token: text is masked
   float lse = lse_ts;
   if (!ts_only) {
     MaxSum all = text;
     ms_merge(all, ts.m, ts.s);
-    lse = all.m == -INFINITY ? -INFINITY : all.m + logf(all.s);
+    lse = all.s == 0.f ? -INFINITY : (all.m + log2f(all.s)) / LOG2E;
   }
-  // ---- pass 2: per-thread top kc (sorted, registers)
-  float lv[BC_KC];
-  int li[BC_KC];
+  // ---- merge the 16 warp lists of the chosen kind: warp 0 alone, every lane owns up to MERGE_PER_LANE entries,
+  // kc rounds of a warp arg-max (the other 15 warps are done)
+  if (wid != 0) return;
+  constexpr int MERGE_PER_LANE = (BC_WARPS * BC_KC + 31) / 32;
+  float mv[MERGE_PER_LANE];
+  int mi[MERGE_PER_LANE];
 #pragma unroll
-  for (int j = 0; j < BC_KC; ++j) { lv[j] = -INFINITY; li[j] = 0x7fffffff; }
-  for (int i0 = tid * 4; i0 < p.n_vocab; i0 += BC_THREADS * 4) {
-    const float4 x4 = *reinterpret_cast<const float4*>(lg + i0);
-    const uint32_t sup4 = load_suppress4(p.suppress, i0, p.n_vocab);
-    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int i = i0 + e;
-      const float x = xs[e];
-      if (!rule_allows(rs, i, ((sup4 >> (8 * e)) & 0xffu) != 0) || (ts_only && i < tb)) continue;
-      bool gt_last = false;   // x beats the thread's current kc-th value (indices ascend, so ties stay behind)
-#pragma unroll
-      for (int j = 0; j < BC_KC; ++j)
-        if (j == kc - 1) gt_last = x > lv[j];
-      if (!gt_last) continue;
-#pragma unroll
-      for (int j = BC_KC - 1; j >= 0; --j) {
-        if (j < kc) {
-          if (j > 0 && x > lv[j - 1]) { lv[j] = lv[j - 1]; li[j] = li[j - 1]; }
-          else if (x > lv[j]) { lv[j] = x; li[j] = i; }
-        }
-      }
+  for (int k = 0; k < MERGE_PER_LANE; ++k) {
+    const int ent = lane + 32 * k;
+    mv[k] = -INFINITY;
+    mi[k] = 0x7fffffff;
+    if (ent < BC_WARPS * kc) {
+      const WarpList& src = lists[ts_only ? 1 : 0][ent / kc];
+      mv[k] = src.v[ent % kc];
+      mi[k] = src.i[ent % kc];
     }
   }
-  // ---- kc rounds of block arg-max over the threads' list heads
   const float cum = p.bm.cum[row];
-  int head = 0;
   for (int r = 0; r < kc; ++r) {
-    float v = -INFINITY;
-    int idx = 0x7fffffff;
+    float bv = mv[0];
+    int bi = mi[0];
 #pragma unroll
-    for (int j = 0; j < BC_KC; ++j)
-      if (j == head) { v = lv[j]; idx = li[j]; }
-    float bv = v;
-    int bi = idx;
+    for (int k = 1; k < MERGE_PER_LANE; ++k)
+      if (cand_before(mv[k], mi[k], bv, bi)) { bv = mv[k]; bi = mi[k]; }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float ov = __shfl_xor_sync(FULL_MASK, bv, o);
       const int oi = __shfl_xor_sync(FULL_MASK, bi, o);
       if (cand_before(ov, oi, bv, bi)) { bv = ov; bi = oi; }
     }
-    if (lane == 0) { win_v[r & 1][wid] = bv; win_i[r & 1][wid] = bi; }
-    __syncthreads();
-    bv = win_v[r & 1][0]; bi = win_i[r & 1][0];
-    for (int w = 1; w < BC_THREADS / 32; ++w)
-      if (cand_before(win_v[r & 1][w], win_i[r & 1][w], bv, bi)) { bv = win_v[r & 1][w]; bi = win_i[r & 1][w]; }
-    if (bi != 0x7fffffff && bi == idx) ++head;   // every token index belongs to exactly one thread
-    if (tid == 0) {
+#pragma unroll
+    for (int k = 0; k < MERGE_PER_LANE; ++k)
+      if (bi != 0x7fffffff && mi[k] == bi) { mv[k] = -INFINITY; mi[k] = 0x7fffffff; }   // an index sits in one list only
+    if (lane == 0) {
       const bool none = bi == 0x7fffffff;
       p.bm.cand_score[(long long)row * kc + r] = none ? -INFINITY : cum + (bv - lse);
       p.bm.cand_tok[(long long)row * kc + r] = none ? p.eot : bi;
