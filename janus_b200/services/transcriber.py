@@ -2,6 +2,8 @@
 :10-91): same constructor (`model_size='base.en'`), `transcribe_buffer(audio_buffer) -> str` with the
 same coercions, the same `[::3]` 48 kHz -> 16 kHz decimation (fused into the log-mel kernel's loads),
 greedy decode (beam_size=1, language 'en'), and the same `' '.join(seg.text.strip()).strip()` assembly.
+`beam_size` is an optional extra constructor argument (default 1 = what the reference passes at :55); a value > 1
+decodes with that many beams per window (BASELINE configs[3]) through janus_whisper_decode_beam_step.
 
 The reference loads pretrained weights from the HF hub through faster-whisper; nothing is downloadable
 here, so by default the named architecture is randomly initialised from a fixed seed (set
@@ -27,7 +29,11 @@ MAX_NEW_TOKENS = 448          # faster-whisper: max_length=448 (DecodeSession ca
 
 
 class Transcriber:
-    def __init__(self, model_size: str = 'base.en', weights: dict | None = None, device=None) -> None:
+    def __init__(self, model_size: str = 'base.en', weights: dict | None = None, device=None,
+                 beam_size: int = 1) -> None:
+        if not 1 <= beam_size <= 8:
+            raise ValueError("beam_size must be in 1 .. 8")
+        self.beam_size = beam_size
         if model_size not in PRESETS:
             raise ValueError(f"unknown Whisper model size {model_size!r}; known: {sorted(PRESETS)}")
         self.dims = PRESETS[model_size]
@@ -42,7 +48,7 @@ class Transcriber:
     def _session(self, batch: int) -> DecodeSession:
         s = self._sessions.get(batch)
         if s is None:
-            s = DecodeSession(self.model, batch, MAX_NEW_TOKENS)
+            s = DecodeSession(self.model, batch, MAX_NEW_TOKENS, beam=self.beam_size if self.beam_size > 1 else 0)
             self._sessions[batch] = s
         return s
 
@@ -73,7 +79,7 @@ class Transcriber:
                     done = int(ses.n_done.item())
                     if done >= len(windows):
                         break
-            tokens = ses.tokens[:, ses.n_prompt:].cpu().numpy()
+            tokens = (ses.finalize()[0] if ses.beam else ses.tokens[:, ses.n_prompt:]).cpu().numpy()
         text_parts = []
         for row in tokens:
             text_parts.extend(split_text_segments(row, self.spec))

@@ -140,3 +140,31 @@ def test_semantic_encoder_latent_lanes_match_kv_lanes():
         assert torch.equal(r.tags, g_)
         agree = float((r.tokens == t).float().mean())
         assert agree >= 0.99, agree
+
+
+def test_transcriber_beam_size_5_matches_oracle_beam_search(monkeypatch):
+    """`Transcriber(beam_size=5)` (optional extra argument; the reference passes beam_size=1) against the oracle's
+    beam search from the same audio, capped at 24 sampled tokens on both sides so that the CPU oracle stays fast.
+    Asserted when the oracle's best / second-best normalised scores are more than 0.05 apart."""
+    import janus_b200.services.transcriber as T
+    from janus_b200.pipeline import join_segments, split_text_segments
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    monkeypatch.setattr(T, "MAX_NEW_TOKENS", 24)
+    tr = T.Transcriber('tiny', beam_size=5)
+    W = init_random_weights(tr.dims, seed=0, profile="confident")
+    x48 = make_clips(1, 6.0, 48000, seed=21).numpy()[0]
+    text = tr.transcribe_buffer(x48)
+    assert isinstance(text, str) and len(text) > 0
+    with torch.no_grad():
+        mel = torch.from_numpy(log_mel_window(x48[::3], tr.dims.n_mels))[None]
+        toks, lp, pools, _ = R.beam_decode(W, tr.dims, tr.spec, R.encode(W, tr.dims, mel), 24, beam_size=5,
+                                           return_all=True)
+    ranked = sorted((p[1] / max(p[2], 1) for p in pools[0]), reverse=True)
+    if len(ranked) < 2 or ranked[0] - ranked[1] > 0.05:
+        assert text == join_segments(split_text_segments(toks[0].tolist(), tr.spec))
+    # greedy and beam transcribers are independent objects with the reference's zero-argument construction
+    with pytest.raises(ValueError):
+        T.Transcriber('tiny', beam_size=9)
