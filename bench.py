@@ -350,6 +350,10 @@ def main() -> None:
     ap.add_argument("--ref-windows", type=int, default=2, help="windows per CPU reference step (stt_prosody)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.beam and args.batch == 1024 and args.lane_batch == 1024:
+        # beam search decodes from per-window K/V caches (55 MB per window for Whisper-small, one pass serves all beams)
+        # and beam x the self-attention rows: 512-window lanes keep two lanes inside 180 GB
+        args.batch = args.lane_batch = 512
     if args.workload == "prosody":
         (run_reference_prosody if args.impl == "reference" else run_gpu_prosody)(args)
     else:
