@@ -86,8 +86,9 @@ def run_reference_stt(args) -> None:
         v, detail = cpu_stt_prosody(args, n, cores)
         vals.append(v)
     value = float(np.mean(vals))
+    dec = f"beam-{args.beam}" if getattr(args, "beam", 0) else "greedy"
     sample = (f"{n} windows x {args.clip_seconds:g} s per step: numpy log-mel + fp32 PyTorch Whisper-{args.model} oracle "
-              f"({cores} threads) greedy {args.max_new_tokens} tokens + YIN oracle + packets; faster-whisper / "
+              f"({cores} threads) {dec} {args.max_new_tokens} tokens + YIN oracle + packets; faster-whisper / "
               "CTranslate2 / aubio are not installable on this box (no network)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
@@ -115,7 +116,8 @@ def run_gpu_stt(args) -> None:
         v, detail = cpu_stt_prosody(args, 1, cores)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": f"1 window x {seconds:g} s: numpy log-mel + fp32 PyTorch Whisper-{args.model} oracle "
-                                  f"({cores} threads) greedy {args.max_new_tokens} tokens + YIN oracle + packet", **detail}
+                                  f"({cores} threads) {'beam-%d' % args.beam if getattr(args, 'beam', 0) else 'greedy'} "
+                                  f"{args.max_new_tokens} tokens + YIN oracle + packet", **detail}
 
     import torch
     import torch.distributed as dist
