@@ -161,6 +161,219 @@ dec_self_attn_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16*
 }
 
 // ------------------------------------------------------------------------------------------
+// causal self-attention for beam search: one warp per (WINDOW, head) serves all K beams. The beams of a window
+// descend from a common ancestor: for positions j < c (c = first position where their indirection entries differ;
+// if all beams use the same slot at j they share everything before j) a K / V row is loaded ONCE and used by all K
+// queries; only the last pos + 1 - c positions are read per beam. dec_self_attn_kernel<true> re-reads the shared
+// prefix once per beam (the duplicates hit L2, but at position ~115 it still costs 12 x 0.158 ms of an 8.6 ms step
+// for 2560 rows of Whisper-small).
+// ------------------------------------------------------------------------------------------
+constexpr int SB_WARPS = 4;
+
+template <int K>
+__global__ void __launch_bounds__(SB_WARPS * 32)
+dec_self_attn_beam_kernel(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos_p, int d,
+                          int n_ctx, int H, int n_items, __nv_bfloat16* out, const uint8_t* indir) {
+  extern __shared__ float sb_smem[];   // per warp: ps[K][n_ctx], qs[K][64]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  pdl_wait();
+  const int item = blockIdx.x * SB_WARPS + warp;
+  if (item >= n_items) return;
+  float* ps = sb_smem + (size_t)warp * K * (n_ctx + DH);
+  float* qs = ps + K * n_ctx;
+  const int w = item / H, h = item - w * H;
+  const long long row0 = (long long)w * K;
+  const int pos = *pos_p;
+  const long long slot_stride = (long long)H * n_ctx * DH;                  // elements between two rows' caches
+  __nv_bfloat16* K0 = kc + (row0 * H + h) * (long long)n_ctx * DH;           // slot 0 of this window, this head
+  __nv_bfloat16* V0 = vc + (row0 * H + h) * (long long)n_ctx * DH;
+  // append this step's k, v of every beam to its own slot; stage the scaled queries
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const __nv_bfloat16* src = qkv + (row0 + k) * 3 * d + h * DH;
+    reinterpret_cast<__nv_bfloat162*>(K0 + k * slot_stride + (long long)pos * DH)[lane] =
+        reinterpret_cast<const __nv_bfloat162*>(src + d)[lane];
+    reinterpret_cast<__nv_bfloat162*>(V0 + k * slot_stride + (long long)pos * DH)[lane] =
+        reinterpret_cast<const __nv_bfloat162*>(src + 2 * d)[lane];
+    const float2 qq = __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(src)[lane]);
+    qs[k * DH + 2 * lane] = qq.x * 0.125f;
+    qs[k * DH + 2 * lane + 1] = qq.y * 0.125f;
+  }
+  __syncwarp();
+  const uint8_t* ind = indir + row0 * n_ctx;   // ind[k * n_ctx + j]
+  // common prefix: position pos is always private (every row just appended to its own slot)
+  int c = pos;
+  for (int j = lane; j < pos; j += 32) {
+    const int s0 = ind[j];
+    bool same = true;
+#pragma unroll
+    for (int k = 1; k < K; ++k) same = same && ind[k * n_ctx + j] == s0;
+    if (!same) { c = j; break; }
+  }
+  c = __reduce_min_sync(FULL_MASK, c);
+  const int jg = lane >> 3, c8 = lane & 7;
+  // ---- scores, shared prefix: one key row per 8 lanes, used by all K queries
+  {
+    float qf[K][8];
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) qf[k][i] = qs[k * DH + c8 * 8 + i];
+#pragma unroll 2
+    for (int j0 = 0; j0 < c; j0 += 4) {
+      const int j = j0 + jg;
+      const bool valid = j < c;
+      uint4 u = make_uint4(0, 0, 0, 0);
+      if (valid) u = reinterpret_cast<const uint4*>(K0 + (int)ind[j] * slot_stride)[(long long)j * 8 + c8];
+      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+      float f[8];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 t2 = __bfloat1622float2(hh[e]);
+        f[2 * e] = t2.x;
+        f[2 * e + 1] = t2.y;
+      }
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        float sc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sc = fmaf(f[i], qf[k][i], sc);
+        sc += __shfl_xor_sync(FULL_MASK, sc, 1);
+        sc += __shfl_xor_sync(FULL_MASK, sc, 2);
+        sc += __shfl_xor_sync(FULL_MASK, sc, 4);
+        if (c8 == 0 && valid) ps[k * n_ctx + j] = sc;
+      }
+    }
+    // ---- scores, private tail: per beam
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      for (int j0 = c; j0 <= pos; j0 += 4) {
+        const int j = j0 + jg;
+        const bool valid = j <= pos;
+        uint4 u = make_uint4(0, 0, 0, 0);
+        if (valid) u = reinterpret_cast<const uint4*>(K0 + (int)ind[k * n_ctx + j] * slot_stride)[(long long)j * 8 + c8];
+        const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+        float sc = 0.f;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 t2 = __bfloat1622float2(hh[e]);
+          sc = fmaf(t2.x, qf[k][2 * e], sc);
+          sc = fmaf(t2.y, qf[k][2 * e + 1], sc);
+        }
+        sc += __shfl_xor_sync(FULL_MASK, sc, 1);
+        sc += __shfl_xor_sync(FULL_MASK, sc, 2);
+        sc += __shfl_xor_sync(FULL_MASK, sc, 4);
+        if (c8 == 0 && valid) ps[k * n_ctx + j] = sc;
+      }
+    }
+  }
+  __syncwarp();
+  // ---- softmax per beam
+  float inv[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    float* pk = ps + k * n_ctx;
+    float mx = -INFINITY;
+    for (int j = lane; j <= pos; j += 32) mx = fmaxf(mx, pk[j]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int j = lane; j <= pos; j += 32) {
+      const float p = __expf(pk[j] - mx);
+      pk[j] = p;
+      sum += p;
+    }
+    inv[k] = 1.f / warp_sum(sum);
+  }
+  __syncwarp();
+  // ---- PV: shared prefix rows once for all beams, private tail per beam
+  float o[K][8];
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[k][i] = 0.f;
+#pragma unroll 2
+  for (int j = jg; j < c; j += 4) {
+    const uint4 u = reinterpret_cast<const uint4*>(V0 + (int)ind[j] * slot_stride)[(long long)j * 8 + c8];
+    const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 t2 = __bfloat1622float2(hh[e]);
+      f[2 * e] = t2.x;
+      f[2 * e + 1] = t2.y;
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const float p = ps[k * n_ctx + j];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[k][i] = fmaf(p, f[i], o[k][i]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    for (int j = c + jg; j <= pos; j += 4) {
+      const uint4 u = reinterpret_cast<const uint4*>(V0 + (int)ind[k * n_ctx + j] * slot_stride)[(long long)j * 8 + c8];
+      const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&u);
+      const float p = ps[k * n_ctx + j];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 t2 = __bfloat1622float2(hh[e]);
+        o[k][2 * e] = fmaf(p, t2.x, o[k][2 * e]);
+        o[k][2 * e + 1] = fmaf(p, t2.y, o[k][2 * e + 1]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      o[k][i] += __shfl_xor_sync(FULL_MASK, o[k][i], 8);
+      o[k][i] += __shfl_xor_sync(FULL_MASK, o[k][i], 16);
+    }
+    if (jg == 0) {
+      uint4 wv;
+      __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&wv);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) hh[e] = __floats2bfloat162_rn(o[k][2 * e] * inv[k], o[k][2 * e + 1] * inv[k]);
+      reinterpret_cast<uint4*>(out + (row0 + k) * d + h * DH)[c8] = wv;
+    }
+  }
+}
+
+template <int K>
+static int launch_self_attn_beam(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos, int d,
+                                 int n_ctx, int H, int n_windows, __nv_bfloat16* out, const uint8_t* indir, cudaStream_t st) {
+  const size_t smem = (size_t)SB_WARPS * K * (n_ctx + DH) * sizeof(float);
+  static size_t attr = 0;
+  if (smem > attr && smem > 48 * 1024) {
+    JANUS_CUDA(cudaFuncSetAttribute(dec_self_attn_beam_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = smem;
+  }
+  const int n_items = n_windows * H;
+  JANUS_CUDA(launch_pdl(dec_self_attn_beam_kernel<K>, dim3((n_items + SB_WARPS - 1) / SB_WARPS), dim3(SB_WARPS * 32), smem, st,
+                        qkv, kc, vc, pos, d, n_ctx, H, n_items, out, indir));
+  return JANUS_OK;
+}
+
+// *handled = false: no kernel for this beam width (the caller falls back to dec_self_attn_kernel<true>)
+static int dec_self_attn_beam(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos, int d,
+                              int n_ctx, int H, int n_windows, int beam, __nv_bfloat16* out, const uint8_t* indir,
+                              cudaStream_t st, bool* handled) {
+  *handled = true;
+  switch (beam) {
+    case 2: return launch_self_attn_beam<2>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    case 3: return launch_self_attn_beam<3>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    case 4: return launch_self_attn_beam<4>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    case 5: return launch_self_attn_beam<5>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    case 6: return launch_self_attn_beam<6>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    case 7: return launch_self_attn_beam<7>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    case 8: return launch_self_attn_beam<8>(qkv, kc, vc, pos, d, n_ctx, H, n_windows, out, indir, st);
+    default: *handled = false; return JANUS_OK;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // cross-attention over the encoder states: one CTA per (head, stream); HBM-bound
 // ------------------------------------------------------------------------------------------
 constexpr int XA_THREADS = 192;  // 192 * 8 keys = 1536 >= 1500
@@ -939,7 +1152,19 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
     const janus_dec_layer_t& L = w->layers[l];
     if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st, light))) return rc;
-    if (bm) {
+    static int beam_sa = -1;   // JANUS_BEAM_SA=0: per-row kernel through the indirection instead of the shared-prefix one
+    if (beam_sa < 0) {
+      const char* e = getenv("JANUS_BEAM_SA");
+      beam_sa = e ? atoi(e) : 1;
+    }
+    bool sa_done = false;
+    if (bm && beam_sa &&
+        (rc = dec_self_attn_beam(qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
+                                 static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, H, B / grp, grp,
+                                 att, bm->indir, st, &sa_done)))
+      return rc;
+    if (sa_done) {
+    } else if (bm) {
       JANUS_CUDA(launch_pdl(dec_self_attn_kernel<true>, dim3((H * B + SA_WARPS - 1) / SA_WARPS), dim3(SA_WARPS * 32), 0, st,
                             qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
                             static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride, s->pos, d, self_ld, H, H * B, att,
