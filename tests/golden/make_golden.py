@@ -5,6 +5,10 @@
 * protocol_golden.json  -- produced by IMPORTING THE REFERENCE's own
   /root/reference/backend/common/protocol.py (msgpack is installed here), so these bytes pin the
   packet builder against the real reference.
+* decode_golden.json    -- greedy and beam-5 decodes of the fp32 Whisper oracle (oracle/whisper_ref.py) on seeded
+  weights / synthetic clips at a shrunken architecture: tokens, sums of log-probs, finished-hypothesis lists and
+  whether each window's result is decisive (margins far above bf16 noise). faster-whisper / CTranslate2 are not
+  installable here, so these vectors pin the CUDA decoder against the oracle ("parity unpinned").
 * prosody_golden.npz    -- produced by the CPU oracle (oracle/yin_aubio.c). aubio itself is not
   installable here, so these vectors pin the CUDA kernels against the oracle, not against aubio
   ("parity unpinned" for per-frame f0).
@@ -102,6 +106,60 @@ def make_prosody():
     print("prosody_golden.npz", len(arrays), "arrays")
 
 
+def decode_setup(eot_scale):
+    """Seeded weights (test dims d=128, 2 heads, 2 layers, 'confident' profile), 3 synthetic clips, oracle encoder
+    states. eot_scale: <|endoftext|> embedding = eot_scale x the most frequent token's, so that hypotheses finish at
+    different lengths (None: random weights, which practically never emit eot)."""
+    import torch
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = test_dims(d=128, heads=2, layers=2)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=3, profile="confident")
+    clips = make_clips(3, 30.0, 16000, seed=77).numpy()
+    mel = torch.stack([torch.from_numpy(log_mel_window(c, dims.n_mels)) for c in clips])
+    with torch.no_grad():
+        if eot_scale is not None:
+            g, _ = R.greedy_decode(W, dims, spec, R.encode(W, dims, mel[:1]), 4)
+            E = W["dec.tok_emb"].clone()
+            E[spec.eot] = (eot_scale * E[int(g[0, 1])]).to(torch.bfloat16).float()
+            W = dict(W)
+            W["dec.tok_emb"] = E
+        enc = R.encode(W, dims, mel)
+    return dims, spec, W, enc, R
+
+
+def decode_cases(n_new=16, beam=5):
+    import torch
+    out = {"n_new": n_new, "beam": beam, "cases": {}}
+    for name, eot_scale in (("random", None), ("eot_biased", 0.9)):
+        dims, spec, W, enc, R = decode_setup(eot_scale)
+        with torch.no_grad():
+            g_tok, g_lp, margins = R.greedy_decode(W, dims, spec, enc, n_new, return_margins=True)
+            b_tok, b_lp, pools, finished = R.beam_decode(W, dims, spec, enc, n_new, beam_size=beam, return_all=True)
+        case = {"greedy_tokens": g_tok.tolist(), "greedy_sum_logprob": [round(float(v), 4) for v in g_lp],
+                "greedy_min_margin": [round(float(m[torch.isfinite(m)].min()), 4) for m in margins],
+                "beam_tokens": b_tok.tolist(), "beam_sum_logprob": [round(float(v), 4) for v in b_lp],
+                "beam_decisive": [], "finished": []}
+        for b in range(enc.shape[0]):
+            ranked = sorted((p[1] / max(p[2], 1) for p in pools[b]), reverse=True)
+            case["beam_decisive"].append(bool(len(ranked) < 2 or ranked[0] - ranked[1] > 0.05))
+            case["finished"].append([{"tokens": f[0], "score": round(float(f[1]), 4), "len": f[2]} for f in finished[b]])
+        out["cases"][name] = case
+    return out
+
+
+def make_decode():
+    out = decode_cases()
+    with open(os.path.join(HERE, "decode_golden.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print("decode_golden.json", {k: len(v["beam_tokens"]) for k, v in out["cases"].items()})
+
+
 if __name__ == "__main__":
     make_protocol()
     make_prosody()
+    make_decode()

@@ -195,3 +195,50 @@ def test_beam5_many_windows_replica_property(latent):
             n = int(nf[r0])
             assert torch.equal(fin_t[r, :n], fin_t[r0, :n]) and torch.equal(fin_s[r, :n], fin_s[r0, :n])
     assert int(nf.sum()) > 0
+
+
+@pytest.mark.parametrize("case", ["random", "eot_biased"])
+@pytest.mark.parametrize("latent", [False, True])
+def test_decode_matches_committed_golden_vectors(case, latent):
+    """Device greedy and beam-5 decodes against the committed golden vectors (tests/golden/decode_golden.json): greedy
+    tokens of every window; beam tokens / sums of log-probs where the golden result is decisive; finished lists
+    where their scores are SCORE_MARGIN apart."""
+    import json
+    import os
+    import sys
+    from janus_b200.whisper.engine import DecodeSession, WhisperEngine
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, here)
+    try:
+        import make_golden
+    finally:
+        sys.path.remove(here)
+    gold = json.load(open(os.path.join(here, "decode_golden.json")))
+    g = gold["cases"][case]
+    dims, spec, W, enc_ref, R = make_golden.decode_setup(None if case == "random" else 0.9)
+    eng = WhisperEngine(dims, W, torch.device("cuda", 0))
+    enc = enc_ref.to(torch.bfloat16).cuda().contiguous()
+    n_new, K = gold["n_new"], gold["beam"]
+    gs = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=n_new, latent=latent)
+    gt, glp = gs.decode(enc)
+    bs = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=n_new, latent=latent, beam=K)
+    bt, blp = bs.decode(enc)
+    torch.cuda.synchronize()
+    gt, bt = gt.cpu().tolist(), bt.cpu().tolist()
+    # greedy: tokens up to (and including) the first eot are the contract; the oracle pads with eot afterwards
+    for b in range(enc.shape[0]):
+        ref = g["greedy_tokens"][b]
+        n = ref.index(spec.eot) + 1 if spec.eot in ref else len(ref)
+        assert gt[b][:n] == ref[:n], (b, gt[b], ref)
+        assert abs(float(glp[b]) - g["greedy_sum_logprob"][b]) <= LP_TOL
+        if g["beam_decisive"][b]:
+            assert bt[b] == g["beam_tokens"][b], (b, bt[b], g["beam_tokens"][b])
+            assert abs(float(blp[b]) - g["beam_sum_logprob"][b]) <= LP_TOL
+        fin = g["finished"][b]
+        scores = [f["score"] for f in fin]
+        if all(abs(scores[i] - scores[j]) > SCORE_MARGIN for i in range(len(scores)) for j in range(i + 1, len(scores))):
+            assert int(bs.n_fin[b]) == len(fin)
+            ft, fl = bs.fin_tokens[b].cpu().tolist(), bs.fin_len[b].cpu().tolist()
+            for j, f in enumerate(fin):
+                assert fl[j] == f["len"] and ft[j][bs.n_prompt:bs.n_prompt + f["len"]] == f["tokens"]
+    assert any(g["beam_decisive"])

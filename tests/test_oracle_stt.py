@@ -159,3 +159,28 @@ def test_beam_step_select_walk():
     # fewer live candidates than beams: the remaining slots are dead beams
     nxt, fin = beam_step_select([(-1.0, 0, 3), (ninf, 1, 4), (ninf, 1, 5)], 2, eot)
     assert nxt == [(-1.0, 0, 3), (ninf, 1, eot)] and fin == []
+
+
+def test_decode_oracle_reproduces_golden_vectors():
+    """tests/golden/decode_golden.json (greedy + beam-5 decodes, generated by tests/golden/make_golden.py) pins the
+    Whisper oracle against drift: same seeds -> same tokens, finished lists and scores."""
+    import json
+    import os
+    import sys
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, here)
+    try:
+        import make_golden
+    finally:
+        sys.path.remove(here)
+    gold = json.load(open(os.path.join(here, "decode_golden.json")))
+    now = make_golden.decode_cases(gold["n_new"], gold["beam"])
+    for name, g in gold["cases"].items():
+        n = now["cases"][name]
+        assert n["greedy_tokens"] == g["greedy_tokens"], name
+        assert n["beam_tokens"] == g["beam_tokens"], name
+        assert n["beam_decisive"] == g["beam_decisive"], name
+        for a, b in zip(n["beam_sum_logprob"] + n["greedy_sum_logprob"], g["beam_sum_logprob"] + g["greedy_sum_logprob"]):
+            assert abs(a - b) <= 2e-3
+        for fa, fb in zip(n["finished"], g["finished"]):
+            assert [f["tokens"] for f in fa] == [f["tokens"] for f in fb] and [f["len"] for f in fa] == [f["len"] for f in fb]
