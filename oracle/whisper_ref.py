@@ -11,7 +11,8 @@ max_initial_timestamp_index=50, max_length 448.
 
 PARITY UNPINNED against faster-whisper/CTranslate2 (not installable offline; the reference's tests mock
 the model). Cross-checked against the independent HF `transformers` Whisper implementation in
-tests/test_oracle_stt.py (same weights, fp32, encoder states and teacher-forced logits).
+tests/test_oracle_stt.py (same weights, fp32, encoder states and teacher-forced logits; beam_decode against HF's
+generic beam search with this module's logit rules as a renormalising LogitsProcessor).
 """
 from __future__ import annotations
 

@@ -184,3 +184,46 @@ def test_decode_oracle_reproduces_golden_vectors():
             assert abs(a - b) <= 2e-3
         for fa, fb in zip(n["finished"], g["finished"]):
             assert [f["tokens"] for f in fa] == [f["tokens"] for f in fb] and [f["len"] for f in fa] == [f["len"] for f in fb]
+
+
+def test_beam_oracle_matches_hf_transformers_beam_search():
+    """Independent cross-check of the oracle's beam search (beam pruning over beam x vocab, cumulative log-probs of the
+    RENORMALISED rule-filtered distribution, ranking by sum / length): HF transformers' generic `generate(num_beams=5)`
+    on the same weights, with the oracle's logit rules plugged in as a LogitsProcessor that renormalises (HF applies
+    processors after its own log-softmax and would otherwise accumulate unnormalised scores, unlike OpenAI Whisper /
+    CTranslate2). Random weights do not emit <|endoftext|>, so this pins the pruning / ranking, not the
+    finished-hypothesis bookkeeping (which differs between HF and OpenAI by design)."""
+    import torch
+    from transformers.generation import GenerationMixin, LogitsProcessor, LogitsProcessorList
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    dims = test_dims(d=64, heads=1, layers=1)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=5, profile="diverse")
+    hf = _to_hf(W, dims)
+    torch.manual_seed(0)
+    mel = torch.randn(2, dims.n_mels, 3000) * 0.5
+    n_new, K = 8, 5
+    with torch.no_grad():
+        tok, lp = R.beam_decode(W, dims, spec, R.encode(W, dims, mel), n_new, beam_size=K)
+    sup = R.suppress_mask_for(spec)
+    n_prompt = len(spec.sot_sequence)
+
+    class Rules(LogitsProcessor):
+        def __call__(self, input_ids, scores):
+            out = scores.clone()
+            for r in range(scores.shape[0]):
+                out[r] = torch.log_softmax(R.apply_logit_rules(scores[r], input_ids[r, n_prompt:].tolist(), spec, sup), -1)
+            return out
+
+    gc = transformers.GenerationConfig(num_beams=K, max_new_tokens=n_new, do_sample=False, length_penalty=1.0,
+                                       early_stopping=False, eos_token_id=spec.eot, pad_token_id=spec.eot,
+                                       decoder_start_token_id=spec.sot_sequence[0], num_return_sequences=1,
+                                       output_scores=True, return_dict_in_generate=True)
+    prompt = torch.tensor([list(spec.sot_sequence)] * mel.shape[0])
+    with torch.no_grad():
+        out = GenerationMixin.generate(hf, input_features=mel, decoder_input_ids=prompt, generation_config=gc,
+                                       attention_mask=None, logits_processor=LogitsProcessorList([Rules()]))
+    assert out.sequences[:, n_prompt:].tolist() == tok.tolist()
+    assert torch.allclose(out.sequences_scores, lp / n_new, atol=1e-3)
