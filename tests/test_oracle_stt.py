@@ -227,3 +227,50 @@ def test_beam_oracle_matches_hf_transformers_beam_search():
                                        attention_mask=None, logits_processor=LogitsProcessorList([Rules()]))
     assert out.sequences[:, n_prompt:].tolist() == tok.tolist()
     assert torch.allclose(out.sequences_scores, lp / n_new, atol=1e-3)
+
+
+@pytest.mark.parametrize("vocab", [51865, 51864])
+def test_logit_rules_match_hf_whisper_logits_processors(vocab):
+    """The decode-time rules (SuppressBlank, SuppressTokens, ApplyTimestampRules incl. max_initial_timestamp and the
+    "timestamps outweigh every text token" rule) are recalled semantics of faster-whisper / openai-whisper.
+    HF transformers ships an independent implementation of the same rules (SuppressTokensAtBegin + SuppressTokens +
+    WhisperTimeStampLogitsProcessor): on arbitrary token histories and logits the two must forbid exactly the same
+    tokens. The CUDA kernels (dec_pick_kernel, dec_beam_cand_kernel) are tested against the oracle's rules."""
+    import numpy as np
+    import torch
+    from transformers.generation.logits_process import (SuppressTokensAtBeginLogitsProcessor, SuppressTokensLogitsProcessor,
+                                                        WhisperTimeStampLogitsProcessor)
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from oracle import whisper_ref as R
+    spec = tokenizer_spec(test_dims(vocab=vocab))
+    n_prompt = len(spec.sot_sequence)
+    gc = transformers.GenerationConfig(eos_token_id=spec.eot, no_timestamps_token_id=spec.no_timestamps,
+                                       max_initial_timestamp_index=spec.max_initial_timestamp_index)
+    chain = [SuppressTokensAtBeginLogitsProcessor([spec.blank, spec.eot], n_prompt),
+             SuppressTokensLogitsProcessor(list(spec.suppress_ids)),
+             WhisperTimeStampLogitsProcessor(gc, n_prompt)]
+    sup = R.suppress_mask_for(spec)
+    rng = np.random.default_rng(0)
+    tb = spec.timestamp_begin
+    fired = 0
+    for _ in range(200):
+        gen = []
+        for _ in range(int(rng.integers(0, 9))):   # arbitrary mixtures of text tokens, timestamps and specials
+            r = rng.random()
+            if r < 0.45:
+                gen.append(int(rng.integers(0, spec.eot)))
+            elif r < 0.9:
+                gen.append(int(rng.integers(tb, spec.n_vocab)))
+            else:
+                gen.append(int(rng.integers(spec.eot, tb)))
+        logits = torch.from_numpy(rng.standard_normal(spec.n_vocab).astype(np.float32)) * float(rng.choice([0.5, 3.0, 10.0]))
+        if rng.random() < 0.3:
+            logits[tb:] += 4.0   # lets the "timestamps outweigh text" rule fire
+        ours = R.apply_logit_rules(logits, gen, spec, sup)
+        sc = logits.clone()[None]
+        ids = torch.tensor([list(spec.sot_sequence) + gen])
+        for p in chain:
+            sc = p(ids, sc)
+        assert torch.equal(torch.isinf(ours), torch.isinf(sc[0])), gen
+        fired += int(bool(torch.isinf(ours[:tb]).all()) and len(gen) > 0)
+    assert fired > 0
