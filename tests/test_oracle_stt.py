@@ -253,7 +253,7 @@ def test_logit_rules_match_hf_whisper_logits_processors(vocab):
     rng = np.random.default_rng(0)
     tb = spec.timestamp_begin
     fired = 0
-    for _ in range(200):
+    for _ in range(100):
         gen = []
         for _ in range(int(rng.integers(0, 9))):   # arbitrary mixtures of text tokens, timestamps and specials
             r = rng.random()
