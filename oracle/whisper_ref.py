@@ -11,8 +11,9 @@ max_initial_timestamp_index=50, max_length 448.
 
 PARITY UNPINNED against faster-whisper/CTranslate2 (not installable offline; the reference's tests mock
 the model). Cross-checked against the independent HF `transformers` Whisper implementation in
-tests/test_oracle_stt.py (same weights, fp32, encoder states and teacher-forced logits; beam_decode against HF's
-generic beam search with this module's logit rules as a renormalising LogitsProcessor).
+tests/test_oracle_stt.py (same weights, fp32): encoder states and teacher-forced logits; apply_logit_rules against HF's
+own Whisper logits processors (identical forbidden sets); greedy_decode against HF generate with those processors (token
+for token); beam_decode against HF's generic beam search with this module's rules as a renormalising LogitsProcessor.
 """
 from __future__ import annotations
 

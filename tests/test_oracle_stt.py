@@ -274,3 +274,38 @@ def test_logit_rules_match_hf_whisper_logits_processors(vocab):
         assert torch.equal(torch.isinf(ours), torch.isinf(sc[0])), gen
         fired += int(bool(torch.isinf(ours[:tb]).all()) and len(gen) > 0)
     assert fired > 0
+
+
+def test_greedy_oracle_matches_hf_generate_end_to_end():
+    """Whole greedy decode, oracle vs HF: HF's Whisper model (same weights) + HF's own Whisper logits processors +
+    HF's greedy loop must emit the oracle's tokens (fp32 both; asserted where the oracle's top-1 margin > 1e-3)."""
+    import torch
+    from transformers.generation import GenerationMixin, LogitsProcessorList
+    from transformers.generation.logits_process import (SuppressTokensAtBeginLogitsProcessor, SuppressTokensLogitsProcessor,
+                                                        WhisperTimeStampLogitsProcessor)
+    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    dims = test_dims(d=64, heads=1, layers=2)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=9, profile="diverse")
+    hf = _to_hf(W, dims)
+    torch.manual_seed(1)
+    mel = torch.randn(3, dims.n_mels, 3000) * 0.5
+    n_new, n_prompt = 20, len(spec.sot_sequence)
+    with torch.no_grad():
+        tok, lp, margins = R.greedy_decode(W, dims, spec, R.encode(W, dims, mel), n_new, return_margins=True)
+    gc = transformers.GenerationConfig(eos_token_id=spec.eot, pad_token_id=spec.eot, no_timestamps_token_id=spec.no_timestamps,
+                                       max_initial_timestamp_index=spec.max_initial_timestamp_index, num_beams=1,
+                                       do_sample=False, max_new_tokens=n_new, decoder_start_token_id=spec.sot_sequence[0])
+    chain = LogitsProcessorList([SuppressTokensAtBeginLogitsProcessor([spec.blank, spec.eot], n_prompt),
+                                 SuppressTokensLogitsProcessor(list(spec.suppress_ids)),
+                                 WhisperTimeStampLogitsProcessor(gc, n_prompt)])
+    prompt = torch.tensor([list(spec.sot_sequence)] * mel.shape[0])
+    with torch.no_grad():
+        out = GenerationMixin.generate(hf, input_features=mel, decoder_input_ids=prompt, generation_config=gc,
+                                       logits_processor=chain)
+    got = out[:, n_prompt:]
+    assert float(margins.min()) > 1e-3, "pick another seed: the oracle itself is at a tie"
+    n = min(got.shape[1], n_new)
+    assert got[:, :n].tolist() == tok[:, :n].tolist()
