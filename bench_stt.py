@@ -314,8 +314,8 @@ def run_gpu_stt(args) -> None:
         traffic = None   # dram bytes of one launch from the committed ncu --set full capture, if it is this launch shape
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "r01_xlat_traffic.json" if latent else
-                                             "r01_xattn_traffic.json")))
-            if (tj["lane_batch"], tj["n_heads"], tj["n_ctx"]) == (lb, H, T) and beam == 1:
+                                             ("r01_xattn_beam_traffic.json" if beam > 1 else "r01_xattn_traffic.json"))))
+            if (tj["lane_batch"], tj["n_heads"], tj["n_ctx"], tj.get("beam", 1)) == (lb, H, T, beam):
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
         except Exception:  # noqa: BLE001
             pass
