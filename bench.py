@@ -349,6 +349,8 @@ def main() -> None:
     ap.add_argument("--ref-clips", type=int, default=0)
     ap.add_argument("--ref-windows", type=int, default=2, help="windows per CPU reference step (stt_prosody)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--parity-windows", type=int, default=4,
+                    help="windows of the timed batch copied back and checked against the CPU oracle (N = 1 only)")
     args = ap.parse_args()
     if args.beam and args.batch == 1024 and args.lane_batch == 1024:
         # beam search decodes from per-window K/V caches (55 MB per window for Whisper-small, one pass serves all beams)

@@ -60,6 +60,8 @@ class EncodeResult:
     sum_logprob: torch.Tensor   # fp32 [B]
     tags: torch.Tensor          # uint8 [B, 2] (device)
     events: list                # one per lane: recorded after the lane wrote its rows
+    mean_f0: torch.Tensor | None = None   # fp32 [B]: mean f0 of the voiced hops in Hz (0 = none voiced)
+    rms: torch.Tensor | None = None       # fp32 [B]: stream RMS (prosody.py:67)
 
     def wait(self, stream: torch.cuda.Stream | None = None) -> "EncodeResult":
         st = stream if stream is not None else torch.cuda.current_stream(self.tokens.device)
@@ -161,7 +163,9 @@ class SemanticEncoder:
             self.result_slots = -(-self.n_lanes // self.lanes_per_call) + 1
             self._results = [(torch.zeros((batch, self.max_new), dtype=torch.int32, device=self.device),
                               torch.zeros(batch, dtype=torch.float32, device=self.device),
-                              torch.zeros((batch, 2), dtype=torch.uint8, device=self.device))
+                              torch.zeros((batch, 2), dtype=torch.uint8, device=self.device),
+                              torch.zeros(batch, dtype=torch.float32, device=self.device),
+                              torch.zeros(batch, dtype=torch.float32, device=self.device))
                              for _ in range(self.result_slots)]
             self._slot = 0
         self._plans: dict = {}
@@ -218,7 +222,7 @@ class SemanticEncoder:
         assert len(lengths) == self.batch
         lb = self.lane_batch
         dev = self.device
-        tokens, sum_lp, tags = self._results[self._slot]
+        tokens, sum_lp, tags, mean_f0, rms = self._results[self._slot]
         self._slot = (self._slot + 1) % self.result_slots
         cur = torch.cuda.current_stream(dev)
         ev_in = torch.cuda.Event()
@@ -256,12 +260,14 @@ class SemanticEncoder:
                     tokens[r].copy_(ses.tokens[:, ses.n_prompt:], non_blocking=True)
                     sum_lp[r].copy_(ses.sum_logprob, non_blocking=True)
                 tags[r].copy_(lane.cur_pros["tags"], non_blocking=True)
+                mean_f0[r].copy_(lane.cur_pros["mean_f0"], non_blocking=True)
+                rms[r].copy_(lane.cur_pros["rms"], non_blocking=True)
                 lane.free = torch.cuda.Event()
                 lane.free.record(lane.stream)
                 self._last_decode = lane.free
                 events.append(lane.free)
             start += n
-        return EncodeResult(tokens, sum_lp, tags, events)
+        return EncodeResult(tokens, sum_lp, tags, events, mean_f0, rms)
 
     def synchronize(self) -> None:
         self.enc_stream.synchronize()
@@ -285,8 +291,11 @@ class SemanticEncoder:
                     d_['avg_energy'] = float(avg_energy[i])
         return texts, pack_packets(texts, pros, mode, override_emotion, timestamps)
 
-    def encode_host(self, buffers: list[np.ndarray], timestamps=None):
-        """Host buffers in, packets out (H2D + kernels + D2H + MessagePack). Synchronises."""
+    def encode_host(self, buffers: list[np.ndarray], timestamps=None, rich_prosody: bool = False):
+        """Host buffers in, packets out (H2D + kernels + D2H + MessagePack). Synchronises. `rich_prosody` adds the
+        stream's mean voiced f0 / RMS (already on the device: prosody_reduce_kernel) as `avg_pitch_hz` / `avg_energy`
+        to the packet's prosody dict -- the fields the reference's receiver reads but its sender leaves None
+        (/root/reference/backend/services/engine.py:231-233,554-560); off by default: it changes the bytes."""
         assert len(buffers) == self.batch
         lengths = tuple(len(b) for b in buffers)
         host = torch.empty(max(sum(lengths), 1), dtype=torch.float32, pin_memory=True)
@@ -299,6 +308,9 @@ class SemanticEncoder:
             res = self.encode_device(pcm, lengths, host_pcm=host).wait()
             tok = res.tokens.cpu().numpy()
             tags = res.tags.cpu().numpy()
+            if rich_prosody:
+                return self.to_packets(tok, tags, timestamps, avg_pitch_hz=res.mean_f0.cpu().numpy(),
+                                       avg_energy=res.rms.cpu().numpy())
         return self.to_packets(tok, tags, timestamps)
 
 

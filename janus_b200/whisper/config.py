@@ -50,7 +50,7 @@ PRESETS = {
 }
 
 
-def test_dims(d: int = 128, heads: int = 2, layers: int = 2, n_mels: int = 80, vocab: int = 51865,
+def mini_dims(d: int = 128, heads: int = 2, layers: int = 2, n_mels: int = 80, vocab: int = 51865,
               n_audio_ctx: int = 1500) -> WhisperDims:
     """A shrunken architecture for fast parity tests (same code paths, same vocab layout)."""
     return WhisperDims(f"test-d{d}-l{layers}", n_mels, n_audio_ctx, d, heads, layers, vocab, 448, d, heads, layers)

@@ -148,6 +148,38 @@ def apply_logit_rules(logits: torch.Tensor, generated: list[int], spec: Tokenize
     return lg
 
 
+def apply_logit_rules_batch(logits: torch.Tensor, generated: list[list[int]], spec: TokenizerSpec,
+                            suppress_mask: torch.Tensor, active=None) -> torch.Tensor:
+    """apply_logit_rules() for B sequences at once (same rules, same order, as column-range masks), so that the CPU
+    baseline is not dominated by a per-sequence Python loop. Checked against the scalar function on random
+    histories in tests/test_oracle_stt.py. Rows with active[b] == False are returned unfiltered."""
+    B, V = logits.shape
+    tb, eot = spec.timestamp_begin, spec.eot
+    ninf = float("-inf")
+    lg = logits.clone()
+    col = torch.arange(V)[None, :]
+    n = torch.tensor([len(g) for g in generated])
+    act = torch.ones(B, dtype=torch.bool) if active is None else torch.as_tensor(active, dtype=torch.bool)
+    first = (n == 0) & act
+    last_ts = torch.tensor([len(g) >= 1 and g[-1] >= tb for g in generated]) & act
+    penult_ts = torch.tensor([len(g) < 2 or g[-2] >= tb for g in generated])
+    # the most recent timestamp token so far (-1: none)
+    last_stamp = torch.tensor([next((t for t in reversed(g) if t >= tb), -1) for g in generated])
+    forbid = suppress_mask[None, :] & act[:, None]
+    forbid = forbid | (first[:, None] & ((col == spec.blank) | (col == eot)))
+    forbid = forbid | ((last_ts & penult_ts)[:, None] & (col >= tb))
+    forbid = forbid | ((last_ts & ~penult_ts)[:, None] & (col < eot))
+    floor = torch.where(last_ts & ~penult_ts, last_stamp, last_stamp + 1)
+    forbid = forbid | (((last_stamp >= 0) & act)[:, None] & (col >= tb) & (col < floor[:, None]))
+    forbid = forbid | (first[:, None] & ((col < tb) | (col > tb + spec.max_initial_timestamp_index)))
+    lg[forbid] = ninf
+    lp = torch.log_softmax(lg.float(), dim=-1)
+    ts_lp = torch.logsumexp(lp[:, tb:], dim=-1)
+    max_text = lp[:, :tb].max(dim=-1).values
+    lg[((ts_lp > max_text) & act)[:, None] & (col < tb)] = ninf
+    return lg
+
+
 def suppress_mask_for(spec: TokenizerSpec) -> torch.Tensor:
     m = torch.zeros(spec.n_vocab, dtype=torch.bool)
     m[list(spec.suppress_ids)] = True
@@ -155,7 +187,7 @@ def suppress_mask_for(spec: TokenizerSpec) -> torch.Tensor:
 
 
 def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor, max_new_tokens: int,
-                  stop_at_eot: bool = True, return_margins: bool = False):
+                  stop_at_eot: bool = True, return_margins: bool = False, vectorized: bool = False):
     """Batched greedy decode at temperature 0. Returns tokens [B, max_new_tokens] (eot-padded after
     the first eot), sum of log-probs [B], and optionally the top-1/top-2 margin at every step."""
     B = enc_out.shape[0]
@@ -171,10 +203,12 @@ def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tens
     n_steps = min(max_new_tokens, spec.max_length - len(spec.sot_sequence))
     for t in range(n_steps):
         nxt = torch.full((B,), spec.eot, dtype=torch.long)
+        if vectorized:   # the same rules for all rows at once (apply_logit_rules_batch)
+            lg_all = apply_logit_rules_batch(logits, gen, spec, sup, active=[not d_ for d_ in done])
         for b in range(B):
             if done[b]:
                 continue
-            lg = apply_logit_rules(logits[b], gen[b], spec, sup)
+            lg = lg_all[b] if vectorized else apply_logit_rules(logits[b], gen[b], spec, sup)
             lp = torch.log_softmax(lg, dim=-1)
             top2 = torch.topk(lg, 2)
             tok = int(top2.indices[0])

@@ -112,11 +112,11 @@ def decode_setup(eot_scale):
     different lengths (None: random weights, which practically never emit eot)."""
     import torch
     from janus_b200.synth import make_clips
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
     from oracle.logmel_ref import log_mel_window
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=3, profile="confident")
     clips = make_clips(3, 30.0, 16000, seed=77).numpy()

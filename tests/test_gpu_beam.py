@@ -20,12 +20,12 @@ LP_TOL = 0.15
 
 def _setup(eot_scale=None, d=128, heads=2, layers=2, n_clips=3, seed=3):
     from janus_b200.synth import make_clips
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.engine import WhisperEngine
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
     from oracle.logmel_ref import log_mel_window
-    dims = test_dims(d=d, heads=heads, layers=layers)
+    dims = mini_dims(d=d, heads=heads, layers=layers)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=seed, profile="confident")
     if eot_scale is not None:

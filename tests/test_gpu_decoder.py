@@ -18,12 +18,12 @@ MARGIN_TOL = 0.3
 
 def _setup(profile, seed, n_clips=3, layers=2, d=128, heads=2):
     from janus_b200.synth import make_clips
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.engine import WhisperEngine
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
     from oracle.logmel_ref import log_mel_window
-    dims = test_dims(d=d, heads=heads, layers=layers)
+    dims = mini_dims(d=d, heads=heads, layers=layers)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=seed, profile=profile)
     clips = make_clips(n_clips, 30.0, 16000, seed=77).numpy()
@@ -185,10 +185,10 @@ def test_fused_segment_session_matches_oracle():
 def test_fused_segment_matches_per_op_path_many_rows(batch):
     """Several 64-row blocks incl. a ragged one: fused and per-op decode agree (same tokens under confident
     weights, logits within bf16 noise) on random encoder states."""
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.engine import DecodeSession, WhisperEngine
     from janus_b200.whisper.weights import init_random_weights
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     W = init_random_weights(dims, seed=11, profile="confident")
     eng = WhisperEngine(dims, W, torch.device("cuda", 0))
     g = torch.Generator().manual_seed(5)

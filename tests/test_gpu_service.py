@@ -53,10 +53,10 @@ def test_semantic_encoder_packets_match_oracle():
     from janus_b200.pipeline import SemanticEncoder
     from janus_b200.protocol import JanusMode, JanusPacket
     from janus_b200.synth import make_clips
-    from janus_b200.whisper.config import test_dims
+    from janus_b200.whisper.config import mini_dims
     from janus_b200.whisper.weights import init_random_weights
     from oracle.prosody_oracle import ProsodyOracle
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     W = init_random_weights(dims, seed=3, profile="confident")
     B, n_new = 4, 24
     enc = SemanticEncoder(dims, batch=B, max_new_tokens=n_new, weights=W)
@@ -78,9 +78,9 @@ def test_semantic_encoder_lanes_pipelined_calls_are_bit_identical():
     import torch
     from janus_b200.pipeline import SemanticEncoder
     from janus_b200.synth import make_clips
-    from janus_b200.whisper.config import test_dims
+    from janus_b200.whisper.config import mini_dims
     from janus_b200.whisper.weights import init_random_weights
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     W = init_random_weights(dims, seed=3, profile="confident")
     B, n_new = 4, 24
     clips = make_clips(2 * B, 30.0, 16000, seed=5, device="cuda")
@@ -113,9 +113,9 @@ def test_semantic_encoder_latent_lanes_match_kv_lanes():
     import torch
     from janus_b200.pipeline import SemanticEncoder
     from janus_b200.synth import make_clips
-    from janus_b200.whisper.config import test_dims
+    from janus_b200.whisper.config import mini_dims
     from janus_b200.whisper.weights import init_random_weights
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     W = init_random_weights(dims, seed=3, profile="confident")
     B, n_new = 128, 12
     n = 48000   # 3 s clips (every window is padded to 30 s of features)

@@ -92,12 +92,12 @@ def test_logmel_decimation_fused():
 
 @pytest.mark.parametrize("name", ["test", "tiny"])
 def test_encoder_vs_fp32_oracle(name):
-    from janus_b200.whisper.config import PRESETS, test_dims
+    from janus_b200.whisper.config import PRESETS, mini_dims
     from janus_b200.whisper.engine import WhisperEngine
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
     from oracle.logmel_ref import log_mel_window
-    dims = test_dims(d=128, heads=2, layers=2) if name == "test" else PRESETS["tiny"]
+    dims = mini_dims(d=128, heads=2, layers=2) if name == "test" else PRESETS["tiny"]
     W = init_random_weights(dims, seed=3)
     clips = _clips()[:2]
     mel = torch.stack([torch.from_numpy(log_mel_window(c, dims.n_mels)) for c in clips])
@@ -113,12 +113,12 @@ def test_large_v3_shape_end_to_end():
     """BASELINE configs[3] architecture family (d = 1280, 20 heads, 128 mel bins, 51866 tokens) at 1 layer:
     K1 log-mel with 128 filters, encoder vs the fp32 oracle, and greedy tokens from audio under confident
     weights. (The 32-layer model only repeats these blocks.)"""
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.engine import DecodeSession, WhisperEngine
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
     from oracle.logmel_ref import log_mel_window
-    dims = test_dims(d=1280, heads=20, layers=1, n_mels=128, vocab=51866)
+    dims = mini_dims(d=1280, heads=20, layers=1, n_mels=128, vocab=51866)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=4, profile="confident")
     clips = _clips()[:2]

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from janus_b200.synth import make_clips
-from janus_b200.whisper.config import PRESETS, detokenize, test_dims, tokenizer_spec
+from janus_b200.whisper.config import PRESETS, detokenize, mini_dims, tokenizer_spec
 from janus_b200.whisper.weights import init_random_weights
 from oracle import whisper_ref as R
 from oracle.logmel_ref import log_mel_utterance, log_mel_window, mel_filters
@@ -82,7 +82,7 @@ def _to_hf(W, dims):
 
 
 def test_whisper_oracle_matches_hf_transformers():
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=1, profile="diverse")
     torch.manual_seed(0)
@@ -100,7 +100,7 @@ def test_whisper_oracle_matches_hf_transformers():
 
 
 def test_greedy_rules():
-    dims = test_dims(d=128, heads=2, layers=2)
+    dims = mini_dims(d=128, heads=2, layers=2)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=3, profile="diverse")
     mel = torch.randn(1, 80, 3000) * 0.5
@@ -130,10 +130,10 @@ def test_beam_oracle_beam1_is_greedy_and_beam5_never_scores_lower():
     """oracle/whisper_ref.py beam_decode: beam 1 reproduces greedy_decode; the best of 5 beams has a normalised
     score >= the greedy hypothesis (same length here: random weights do not emit eot)."""
     import torch
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
-    dims = test_dims(d=64, heads=1, layers=1)
+    dims = mini_dims(d=64, heads=1, layers=1)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=5, profile="diverse")
     torch.manual_seed(0)
@@ -195,10 +195,10 @@ def test_beam_oracle_matches_hf_transformers_beam_search():
     finished-hypothesis bookkeeping (which differs between HF and OpenAI by design)."""
     import torch
     from transformers.generation import GenerationMixin, LogitsProcessor, LogitsProcessorList
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
-    dims = test_dims(d=64, heads=1, layers=1)
+    dims = mini_dims(d=64, heads=1, layers=1)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=5, profile="diverse")
     hf = _to_hf(W, dims)
@@ -240,9 +240,9 @@ def test_logit_rules_match_hf_whisper_logits_processors(vocab):
     import torch
     from transformers.generation.logits_process import (SuppressTokensAtBeginLogitsProcessor, SuppressTokensLogitsProcessor,
                                                         WhisperTimeStampLogitsProcessor)
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from oracle import whisper_ref as R
-    spec = tokenizer_spec(test_dims(vocab=vocab))
+    spec = tokenizer_spec(mini_dims(vocab=vocab))
     n_prompt = len(spec.sot_sequence)
     gc = transformers.GenerationConfig(eos_token_id=spec.eot, no_timestamps_token_id=spec.no_timestamps,
                                        max_initial_timestamp_index=spec.max_initial_timestamp_index)
@@ -283,10 +283,10 @@ def test_greedy_oracle_matches_hf_generate_end_to_end():
     from transformers.generation import GenerationMixin, LogitsProcessorList
     from transformers.generation.logits_process import (SuppressTokensAtBeginLogitsProcessor, SuppressTokensLogitsProcessor,
                                                         WhisperTimeStampLogitsProcessor)
-    from janus_b200.whisper.config import test_dims, tokenizer_spec
+    from janus_b200.whisper.config import mini_dims, tokenizer_spec
     from janus_b200.whisper.weights import init_random_weights
     from oracle import whisper_ref as R
-    dims = test_dims(d=64, heads=1, layers=2)
+    dims = mini_dims(d=64, heads=1, layers=2)
     spec = tokenizer_spec(dims)
     W = init_random_weights(dims, seed=9, profile="diverse")
     hf = _to_hf(W, dims)
@@ -309,3 +309,41 @@ def test_greedy_oracle_matches_hf_generate_end_to_end():
     assert float(margins.min()) > 1e-3, "pick another seed: the oracle itself is at a tie"
     n = min(got.shape[1], n_new)
     assert got[:, :n].tolist() == tok[:, :n].tolist()
+
+
+def test_vectorized_logit_rules_equal_the_scalar_rules():
+    """apply_logit_rules_batch (used by the timed CPU baseline so that it is not handicapped by a per-sequence Python
+    loop) forbids exactly the same tokens and keeps exactly the same values as apply_logit_rules, on random histories
+    of both vocabulary layouts; greedy_decode(vectorized=True) returns the same tokens."""
+    import random
+    from janus_b200.whisper.config import PRESETS, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    for name in ("tiny", "tiny.en"):
+        dims = PRESETS[name]
+        spec = tokenizer_spec(dims)
+        sup = R.suppress_mask_for(spec)
+        tb = spec.timestamp_begin
+        rnd = random.Random(3)
+        hs = []
+        for _ in range(200):
+            h = []
+            for _ in range(rnd.choice([0, 1, 2, 3, 5, 9])):
+                h.append(rnd.randint(tb, dims.n_vocab - 1) if rnd.random() < 0.4 else rnd.randint(0, spec.eot - 1))
+            hs.append(h)
+        logits = torch.randn(len(hs), dims.n_vocab, generator=torch.Generator().manual_seed(1)) * 3
+        logits[::3, tb:] += 4          # rows where the timestamp mass outweighs every text token
+        got = R.apply_logit_rules_batch(logits, hs, spec, sup)
+        for b, h in enumerate(hs):
+            ref = R.apply_logit_rules(logits[b], h, spec, sup)
+            assert torch.equal(torch.isinf(ref), torch.isinf(got[b])), (name, b, h)
+            keep = ~torch.isinf(ref)
+            assert torch.equal(ref[keep], got[b][keep])
+    dims = mini_dims(d=64, heads=1, layers=1)
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=2, profile="confident")
+    enc = torch.randn(3, dims.n_audio_ctx, dims.n_audio_state, generator=torch.Generator().manual_seed(4))
+    with torch.no_grad():
+        a, la = R.greedy_decode(W, dims, spec, enc, 20)
+        b, lb = R.greedy_decode(W, dims, spec, enc, 20, vectorized=True)
+    assert torch.equal(a, b) and torch.allclose(la, lb)
