@@ -45,9 +45,19 @@ int32_t janus_abi_version(void);
 const char* janus_last_error(void);
 /* 0 when device `dev` can run the kernels (compute capability 10.x), else JANUS_ERR_UNSUPPORTED. */
 int32_t janus_check_device(int32_t dev);
-/* Programmatic dependent launch for the decode-step kernel chain (default on). 0 launches the same
- * kernels fully serialised; returns the previous setting. Process-global; meant for A/B measurements. */
-int32_t janus_set_pdl(int32_t enabled);
+/* Process-wide tunables, set explicitly (nothing in the library reads the environment). value < 0 restores the
+ * built-in default. They select between measured alternates of a kernel, for A/B measurements and so that both
+ * variants can be tested in one process; results are identical within the stated tolerances either way. */
+typedef enum {
+  JANUS_OPT_PDL = 0,                   /* programmatic dependent launch for the decode-step chain (default 1)       */
+  JANUS_OPT_ATT_SPLIT = 1,             /* encoder attention: softmax threads per query row, 1 | 2 (default 1)        */
+  JANUS_OPT_XLAT_STREAM = 2,           /* latent cross-attention: 1 = streaming two-pass kernel even for d <= 768    */
+  JANUS_OPT_XLAT_CTAS = 3,             /* latent cross-attention: cap of the persistent grid, 0 = one CTA per SM     */
+  JANUS_OPT_XA_CTAS_PER_SM = 4,        /* K/V cross-attention: cap of CTAs per SM, 0 = no cap                        */
+  JANUS_OPT_BEAM_SHARED_SELF_ATTN = 5, /* beam search: shared-prefix self-attention kernel (default 1) or per row    */
+  JANUS_OPT_COUNT = 6
+} janus_option_t;
+int32_t janus_set_option(int32_t option, int32_t value);
 
 /* ------------------------------------------------------------------------------------------
  * K4: YIN pitch + per-hop level (bit-exact restatement of aubio's float32 arithmetic)
@@ -104,13 +114,6 @@ int32_t janus_gemm_bf16(const void* A, int64_t lda, int64_t a_batch_stride, cons
 int32_t janus_layernorm_bf16(const void* x, const float* w, const float* b, void* y, int64_t rows, int32_t d,
                              void* stream);
 /* Fused non-causal attention over packed qkv bf16 [n_batch, T, 3*64*n_heads] -> out bf16 [n_batch, T, 64*n_heads]. */
-/* Diagnostic: n dependent LayerNorm launches (PDL chain) issued from C; used to measure launch latency. */
-int32_t janus_debug_ln_chain(const void* x, const float* w, const float* b, void* y, int64_t rows, int32_t d,
-                             int32_t n, void* stream);
-/* Diagnostic: a fused decode segment of n_phases identical linear phases (timing of one phase + grid barrier). */
-int32_t janus_debug_fused_linear(const void* A, const void* W, const float* bias, void* out, const float* ln_w,
-                                 const float* ln_b, int32_t rows, int32_t N, int32_t K, int32_t d, int32_t cfg,
-                                 int32_t n_phases, void* barrier, const int32_t* pos, void* stream);
 int32_t janus_attention_enc_bf16(const void* qkv, void* out, int32_t n_batch, int32_t T, int32_t n_heads,
                                  void* stream);
 
@@ -130,6 +133,22 @@ int32_t janus_logmel_f32(const float* pcm, const int64_t* offsets, const int64_t
                          int32_t decim, int32_t n_mels, const int32_t* mel_start, const int32_t* mel_len,
                          const float* mel_w, int32_t mel_max_len, float* scratch, int32_t* maxbuf,
                          void* mel_bf16_out, float* mel_f32_out, void* stream);
+
+/* The same in two calls, for utterances longer than one 30 s window (faster-whisper computes the features ONCE per
+ * utterance -- one global max-8 clamp floor, a continuous STFT -- and then slices 3000-frame windows at `seek` frames,
+ * advancing seek by the last decoded timestamp; the call site is backend/services/transcriber.py:53-57):
+ *   janus_logmel_utterance_f32  pass 1 over whole utterances: scratch fp32 [n, nf_alloc, n_mels] = log10 mel of up
+ *                               to nf_alloc frames of each utterance (frame count of utterance s:
+ *                               (ceil(len/decim) + 160) / 160), maxbuf int32 [n] = ordered-int key of its maximum;
+ *   janus_logmel_windows_f32    pass 2 for n_windows windows: window w = frames [win_seek[w], +3000) of utterance
+ *                               win_utt[w], clamped to that utterance's max - 8, zero-padded in feature space. */
+int32_t janus_logmel_utterance_f32(const float* pcm, const int64_t* offsets, const int64_t* lengths, int32_t n,
+                                   int32_t decim, int32_t n_mels, const int32_t* mel_start, const int32_t* mel_len,
+                                   const float* mel_w, int32_t mel_max_len, float* scratch, int32_t nf_alloc,
+                                   int32_t* maxbuf, void* stream);
+int32_t janus_logmel_windows_f32(const float* scratch, const int32_t* maxbuf, const int64_t* lengths, int32_t decim,
+                                 int32_t n_mels, int32_t nf_alloc, const int32_t* win_utt, const int32_t* win_seek,
+                                 int32_t n_windows, void* mel_bf16_out, float* mel_f32_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * K2: Whisper encoder (replaces CTranslate2 Whisper.encode reached from transcriber.py:53-57)
@@ -198,10 +217,8 @@ typedef struct {
  * TMEM, < 32 KB shared memory) so that the step can share SMs with the tcgen05 encoder kernels of
  * another stream; requires batch <= 64. */
 #define JANUS_DECODE_LIGHT 1
-/* JANUS_DECODE_FUSED: everything between two cross-attentions runs as one persistent kernel with grid-wide
- * barriers (dec_fused.cu) instead of one kernel per op; needs state->barrier. At most one fused decode
- * chain may be in flight per device at a time (its CTAs wait on each other). */
-#define JANUS_DECODE_FUSED 2
+/* (flag value 2 is retired: the experimental grid-barrier segment kernel was measured slower than the per-op chain
+ * and is no longer part of the library) */
 /* JANUS_DECODE_LATENT: cross-attention reads the encoder states (state->enc_out) instead of per-layer K/V
  * caches -- half the HBM bytes per step, no cross_k / cross_v at all (janus_b200/csrc/dec_xlat.cu). Needs
  * d % 128 == 0, d <= 1024, <= 16 heads, the w_ck_lat / w_cv / b_cv layer weights and state->enc_out / qlat / zlat. */
@@ -231,7 +248,7 @@ typedef struct {
   const void* cross_v;                 /* bf16 [L, batch, H, n_ctx, 64];                   NULL with JANUS_DECODE_LATENT */
   void* x; void* xn; void* qkv; void* att; void* q; void* ff;  /* bf16 [batch, d|d|3d|d|d|4d] */
   float* logits;                       /* fp32 [batch, n_vocab_pad] */
-  uint64_t* barrier;                   /* device counter for JANUS_DECODE_FUSED (zero-initialised once), else NULL */
+  uint64_t* reserved1;                 /* NULL (was the grid-barrier counter of the retired fused segment kernel) */
   const void* enc_out;                 /* JANUS_DECODE_LATENT: bf16 [batch, n_ctx, d] encoder states, else NULL */
   void* qlat;                          /* JANUS_DECODE_LATENT: bf16 [batch, 16, d], zero-initialised once */
   void* zlat;                          /* JANUS_DECODE_LATENT: bf16 [batch, H, d] */

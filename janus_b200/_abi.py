@@ -24,18 +24,18 @@ SIGNATURES = {
     "janus_abi_version": (_I32, []),
     "janus_last_error": (_c.c_char_p, []),
     "janus_check_device": (_I32, [_I32]),
-    "janus_set_pdl": (_I32, [_I32]),
+    "janus_set_option": (_I32, [_I32, _I32]),
     "janus_yin_frames_per_group": (_I32, []),
     "janus_yin_frames_f32": (_I32, [_P, _P, _P, _P, _P, _I32, _I64, _I32, _I32, _I32, _F32, _F32,
                                     _P, _P, _P, _P, _P]),
     "janus_yin_state_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     "janus_prosody_reduce_f32": (_I32, [_P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P]),
     "janus_layernorm_bf16": (_I32, [_P, _P, _P, _P, _I64, _I32, _P]),
-    "janus_debug_ln_chain": (_I32, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),
-    "janus_debug_fused_linear": (_I32, [_P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _I32, _P, _P, _P]),
     "janus_attention_enc_bf16": (_I32, [_P, _P, _I32, _I32, _I32, _P]),
     "janus_logmel_frames_alloc": (_I32, []),
     "janus_logmel_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _P, _P, _P, _P]),
+    "janus_logmel_utterance_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P, _I32, _P, _I32, _P, _P]),
+    "janus_logmel_windows_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _I32, _P, _P, _P]),
     "janus_whisper_encode_workspace_bytes": (_I64, [_P, _I32]),
     "janus_whisper_encode_bf16": (_I32, [_P, _P, _P, _I32, _P, _P, _I64, _P]),
     "janus_dec_linear_bf16": (_I32, [_P, _I32, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _P]),
@@ -51,6 +51,15 @@ SIGNATURES = {
     "janus_gemm_bf16": (_I32, [_P, _I64, _I64, _P, _I64, _P, _I64, _I64, _I32, _I32, _I32, _I32, _I32,
                                _P, _P, _P, _I32, _P]),
 }
+
+
+# janus_option_t (include/janus_b200.h)
+OPT_PDL, OPT_ATT_SPLIT, OPT_XLAT_STREAM, OPT_XLAT_CTAS, OPT_XA_CTAS_PER_SM, OPT_BEAM_SHARED_SELF_ATTN = range(6)
+
+
+def set_option(option: int, value: int) -> None:
+    """Process-wide tunable of the library (value < 0 restores the default); see janus_option_t."""
+    call("janus_set_option", option, value)
 
 
 class JanusNativeError(RuntimeError):
@@ -72,11 +81,11 @@ def lib() -> ctypes.CDLL:
     with _lock:
         if _lib is not None:
             return _lib
-        if not os.path.exists(LIB_PATH):
-            from . import build as _build
-            try:
-                _build.build()
-            except Exception as exc:  # noqa: BLE001
+        from . import build as _build
+        try:
+            _build.build()       # a no-op unless the library is missing or older than its sources
+        except Exception as exc:  # noqa: BLE001
+            if not os.path.exists(LIB_PATH):
                 raise JanusNativeError(
                     f"libjanus_b200.so is missing and could not be built with nvcc: {exc}. "
                     "Run `python -m janus_b200.build`. There is no CPU fallback.") from exc

@@ -10,12 +10,22 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 int g_pdl_enabled = 1;
+// process-wide tunables (janus_set_option): -1 = "use the built-in default" at the site that reads the option
+static int g_options[JANUS_OPT_COUNT] = {-1, -1, -1, -1, -1, -1};
+int option(int opt, int dflt) {
+  const int v = (opt >= 0 && opt < JANUS_OPT_COUNT) ? g_options[opt] : -1;
+  return v < 0 ? dflt : v;
+}
 }  // namespace janus
 
-extern "C" int32_t janus_set_pdl(int32_t enabled) {
-  const int prev = janus::g_pdl_enabled;
-  janus::g_pdl_enabled = enabled != 0;
-  return prev;
+extern "C" int32_t janus_set_option(int32_t opt, int32_t value) {
+  if (opt < 0 || opt >= JANUS_OPT_COUNT) {
+    janus::set_error("janus_set_option: unknown option %d", opt);
+    return JANUS_ERR_INVALID_ARG;
+  }
+  janus::g_options[opt] = value < 0 ? -1 : value;
+  if (opt == JANUS_OPT_PDL) janus::g_pdl_enabled = value != 0;   // default (-1) = on
+  return JANUS_OK;
 }
 
 extern "C" int32_t janus_abi_version(void) { return JANUS_ABI_VERSION; }

@@ -413,12 +413,15 @@ int attention_enc(const __nv_bfloat16* qkv, __nv_bfloat16* out, int n_batch, int
   const uint32_t box[3] = {ATT_DH, 128, 1};
   int rc = make_tmap_bf16(&tm, qkv, 3, dims, str, box);
   if (rc) return rc;
-  static int split = 0;   // threads per query row: JANUS_ATT_SPLIT=1|2 (default ATT_DEFAULT_SPLIT)
-  if (!split) {
-    const char* e = getenv("JANUS_ATT_SPLIT");
-    split = e && atoi(e) >= 1 && atoi(e) <= 2 ? atoi(e) : ATT_DEFAULT_SPLIT;
+  // threads per query row: JANUS_OPT_ATT_SPLIT = 1 | 2 (default ATT_DEFAULT_SPLIT)
+  int split = option(JANUS_OPT_ATT_SPLIT, ATT_DEFAULT_SPLIT);
+  if (split < 1 || split > 2) split = ATT_DEFAULT_SPLIT;
+  static bool attr[64] = {};
+  const int dev = current_device_slot();
+  if (!attr[dev]) {
     JANUS_CUDA(cudaFuncSetAttribute(attention_enc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
     JANUS_CUDA(cudaFuncSetAttribute(attention_enc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    attr[dev] = true;
   }
   const dim3 grid((T + ATT_BQ - 1) / ATT_BQ, n_heads, n_batch);
   const float scale_log2 = 0.125f * 1.4426950408889634f;  // 1/sqrt(64) * log2(e)

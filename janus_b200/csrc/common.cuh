@@ -11,6 +11,10 @@ namespace janus {
 
 // thread-local last-error buffer (defined in abi.cu)
 void set_error(const char* fmt, ...);
+// process-wide tunable `opt` (janus_option_t), or `dflt` when it was never set / reset to -1 (abi.cu)
+int option(int opt, int dflt);
+// index of the current device for per-device caches of kernel attributes (gemm.cu)
+int current_device_slot();
 
 #define JANUS_CHECK_ARG(cond, ...)                 \
   do {                                             \

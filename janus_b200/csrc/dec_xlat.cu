@@ -582,18 +582,11 @@ int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16*
     int rc = make_tmap_bf16(&tq, qlat, 3, dims, str, box);
     if (rc) return rc;
   }
-  static int variant = -1;   // JANUS_XLAT_STREAM=0|1: one-tile ring (d <= 768) or streaming two-pass kernel (default)
-  if (variant < 0) {
-    const char* e = getenv("JANUS_XLAT_STREAM");
-    variant = e ? atoi(e) != 0 : XL_DEFAULT_STREAM;
-  }
+  // JANUS_OPT_XLAT_STREAM: 0 = one-tile ring (d <= 768), 1 = streaming two-pass kernel
+  const int variant = option(JANUS_OPT_XLAT_STREAM, XL_DEFAULT_STREAM);
   const bool stream_variant = variant || d / 64 > XL_MAX_BOXES;   // d > 768: a whole tile does not fit the ring
   int max_ctas = num_sms();
-  static int cap = -1;   // JANUS_XLAT_CTAS=n caps the persistent grid (scaling experiments)
-  if (cap < 0) {
-    const char* e = getenv("JANUS_XLAT_CTAS");
-    cap = e ? atoi(e) : 0;
-  }
+  const int cap = option(JANUS_OPT_XLAT_CTAS, 0);   // n > 0 caps the persistent grid (scaling experiments)
   if (cap > 0 && cap < max_ctas) max_ctas = cap;
   const int grid = n_windows < max_ctas ? n_windows : max_ctas;
   const float scale_log2 = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
@@ -601,20 +594,22 @@ int dec_xlat(const __nv_bfloat16* qlat, const __nv_bfloat16* enc, __nv_bfloat16*
     const int ps = xlat2_pair_slots(d);
     const int tmem_cols = 32 + (d / 128) * XL_HP <= 128 ? 128 : 256;
     const size_t smem = xlat2_smem_bytes(d);
-    static size_t attr2 = 0;
-    if (smem > attr2) {
+    static size_t attr2[64] = {};
+    const int dev = current_device_slot();
+    if (smem > attr2[dev]) {
       JANUS_CUDA(cudaFuncSetAttribute(dec_xlat2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      attr2 = smem;
+      attr2[dev] = smem;
     }
     JANUS_CUDA(launch_pdl(dec_xlat2_kernel, dim3(grid), dim3(XL_THREADS), smem, stream, tx, tq, z, T, d, n_heads,
                           n_windows, scale_log2, ps, tmem_cols, x_group));
     return JANUS_OK;
   }
   const size_t smem = xlat_smem_bytes(d);
-  static size_t attr_bytes = 0;
-  if (smem > attr_bytes) {
+  static size_t attr_bytes[64] = {};
+  const int dev1 = current_device_slot();
+  if (smem > attr_bytes[dev1]) {
     JANUS_CUDA(cudaFuncSetAttribute(dec_xlat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_bytes = smem;
+    attr_bytes[dev1] = smem;
   }
   JANUS_CUDA(launch_pdl(dec_xlat_kernel, dim3(grid), dim3(XL_THREADS), smem, stream, tx, tq, z, T, d, n_heads,
                         n_windows, scale_log2, x_group));

@@ -345,10 +345,11 @@ template <int K>
 static int launch_self_attn_beam(const __nv_bfloat16* qkv, __nv_bfloat16* kc, __nv_bfloat16* vc, const int32_t* pos, int d,
                                  int n_ctx, int H, int n_windows, __nv_bfloat16* out, const uint8_t* indir, cudaStream_t st) {
   const size_t smem = (size_t)SB_WARPS * K * (n_ctx + DH) * sizeof(float);
-  static size_t attr = 0;
-  if (smem > attr && smem > 48 * 1024) {
+  static size_t attr[64] = {};
+  const int dev = current_device_slot();
+  if (smem > attr[dev] && smem > 48 * 1024) {
     JANUS_CUDA(cudaFuncSetAttribute(dec_self_attn_beam_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr = smem;
+    attr[dev] = smem;
   }
   const int n_items = n_windows * H;
   JANUS_CUDA(launch_pdl(dec_self_attn_beam_kernel<K>, dim3((n_items + SB_WARPS - 1) / SB_WARPS), dim3(SB_WARPS * 32), smem, st,
@@ -476,11 +477,7 @@ dec_cross_attn_kernel(const __nv_bfloat16* q, const __nv_bfloat16* __restrict__ 
 // Grid of the cross-attention kernel: one CTA per (stream, head) by default; JANUS_XA_CTAS_PER_SM=n makes it
 // persistent with n CTAs per SM so that tcgen05 CTAs of a concurrent encoder stream always find room.
 static int xa_grid(int n_items) {
-  static int cap = -1;
-  if (cap < 0) {
-    const char* e = getenv("JANUS_XA_CTAS_PER_SM");
-    cap = e ? atoi(e) : 0;
-  }
+  const int cap = option(JANUS_OPT_XA_CTAS_PER_SM, 0);   // > 0: cap the cross-attention grid (overlap experiments)
   if (cap <= 0) return n_items;
   const long long g = (long long)cap * num_sms();
   return n_items < g ? n_items : (int)g;
@@ -638,11 +635,12 @@ template <int NQ, int US, int UV>
 static int launch_cross_attn_beam(const __nv_bfloat16* q, const __nv_bfloat16* kT, const __nv_bfloat16* v, int T, int kv_ld,
                                   int d, int H, int n_streams, __nv_bfloat16* out, cudaStream_t st) {
   const size_t smem = (size_t)NQ * XA_THREADS * 8 * sizeof(float);
-  static bool attr = false;
-  if (!attr) {
+  static bool attr[64] = {};
+  const int dev = current_device_slot();
+  if (!attr[dev]) {
     JANUS_CUDA(cudaFuncSetAttribute(dec_cross_attn_beam_kernel<NQ, US, UV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)smem));
-    attr = true;
+    attr[dev] = true;
   }
   JANUS_CUDA(launch_pdl(dec_cross_attn_beam_kernel<NQ, US, UV>, dim3(xa_grid(H * n_streams)), dim3(XA_THREADS), smem, st, q,
                         kT, v, T, kv_ld, d, H, H * n_streams, out));
@@ -1064,19 +1062,16 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
                                 const janus_decode_state_t* s, const janus_beam_state_t* bm, void* stream_) {
   JANUS_CHECK_ARG(c && w && s, "decode_step: null pointer");
   const int grp = bm ? bm->beam : 1;
-  JANUS_CHECK_ARG(!bm || !(s->flags & (JANUS_DECODE_LIGHT | JANUS_DECODE_FUSED)),
-                  "decode_beam_step: LIGHT / FUSED sessions are greedy only");
+  JANUS_CHECK_ARG(!bm || !(s->flags & JANUS_DECODE_LIGHT), "decode_beam_step: LIGHT sessions are greedy only");
   JANUS_CHECK_ARG(c->d == c->n_heads * 64, "decode_step: head_dim must be 64");
   JANUS_CHECK_ARG(c->n_ctx <= XA_THREADS * 8 && w->kv_ld % 8 == 0 && w->kv_ld >= c->n_ctx && w->kv_ld <= XA_THREADS * 8,
                   "decode_step: n_ctx=%d / kv_ld=%d unsupported", c->n_ctx, w->kv_ld);
   JANUS_CHECK_ARG(w->n_text_ctx <= 512, "decode_step: n_text_ctx must be <= 512");
   const bool light = (s->flags & JANUS_DECODE_LIGHT) != 0;
-  const bool fused = (s->flags & JANUS_DECODE_FUSED) != 0;
   const bool latent = (s->flags & JANUS_DECODE_LATENT) != 0;
-  JANUS_CHECK_ARG(!latent || (!fused && !light && s->enc_out && s->qlat && s->zlat),
-                  "decode_step: JANUS_DECODE_LATENT needs enc_out / qlat / zlat and excludes LIGHT / FUSED");
+  JANUS_CHECK_ARG(!latent || (!light && s->enc_out && s->qlat && s->zlat),
+                  "decode_step: JANUS_DECODE_LATENT needs enc_out / qlat / zlat and excludes LIGHT");
   JANUS_CHECK_ARG(latent || (s->cross_k && s->cross_v), "decode_step: cross_k / cross_v missing");
-  JANUS_CHECK_ARG(!fused || s->barrier, "decode_step: JANUS_DECODE_FUSED needs state->barrier");
   JANUS_CHECK_ARG(!light || s->batch <= 64, "decode_step: JANUS_DECODE_LIGHT needs batch <= 64 (got %d)", s->batch);
   cudaStream_t st = (cudaStream_t)stream_;
   const int B = s->batch, d = c->d, H = c->n_heads, T = c->n_ctx;
@@ -1099,64 +1094,12 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
   const long long rm_stride = (long long)(B / grp) * H * T * DH;
   const long long ck_stride = kv_swapped ? rm_stride : kt_stride;
   const long long cv_stride = kv_swapped ? kt_stride : rm_stride;
-  if (fused) {
-    FusedProgram base = {};
-    base.rows = B; base.d = d; base.n_heads = H; base.pos = s->pos;
-    base.barrier = reinterpret_cast<unsigned long long*>(s->barrier);
-    auto lin = [&](const void* A, int lda, const float* lw, const float* lb, const void* W, const float* bias,
-                   const void* res, void* out, int N, int K, int act, int cfg) {
-      FusedPhase ph = {};
-      ph.type = FZ_LINEAR;
-      ph.lin.A = A; ph.lin.lda = lda; ph.lin.ln_w = lw; ph.lin.ln_b = lb; ph.lin.W = W; ph.lin.bias = bias;
-      ph.lin.residual = res; ph.lin.out = out; ph.lin.N = N; ph.lin.K = K; ph.lin.kc = d; ph.lin.act = act;
-      ph.lin.cfg = cfg;
-      return ph;
-    };
-    auto tail_of = [&](FusedProgram& P, const janus_dec_layer_t& L) {   // ops after layer L's cross-attention
-      P.ph[P.n_phases++] = lin(att, d, nullptr, nullptr, L.w_co, L.b_co, x, x, d, d, ACT_NONE, 0);
-      P.ph[P.n_phases++] = lin(x, d, L.ln2_w, L.ln2_b, L.w_fc1, L.b_fc1, nullptr, ff, 4 * d, d, ACT_GELU, 2);
-      P.ph[P.n_phases++] = lin(ff, 4 * d, nullptr, nullptr, L.w_fc2, L.b_fc2, x, x, d, 4 * d, ACT_NONE, 0);
-    };
-    for (int l = 0; l < c->n_layers; ++l) {
-      const janus_dec_layer_t& L = w->layers[l];
-      FusedProgram P = base;
-      if (l > 0) tail_of(P, w->layers[l - 1]);
-      P.ph[P.n_phases++] = lin(x, d, L.ln1_w, L.ln1_b, L.w_qkv, L.b_qkv, nullptr, qkv, 3 * d, d, ACT_NONE, 1);
-      {
-        FusedPhase ph = {};
-        ph.type = FZ_SELF_ATTN;
-        ph.sa.qkv = qkv;
-        ph.sa.k_cache = static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride;
-        ph.sa.v_cache = static_cast<__nv_bfloat16*>(s->self_v) + l * self_stride;
-        ph.sa.out = att; ph.sa.n_ctx = self_ld;
-        P.ph[P.n_phases++] = ph;
-      }
-      P.ph[P.n_phases++] = lin(att, d, nullptr, nullptr, L.w_o, L.b_o, x, x, d, d, ACT_NONE, 0);
-      P.ph[P.n_phases++] = lin(x, d, L.lnc_w, L.lnc_b, L.w_cq, L.b_cq, nullptr, q, d, d, ACT_NONE, 0);
-      if ((rc = dec_fused_segment(P, st))) return rc;
-      JANUS_CUDA(launch_pdl(dec_cross_attn_kernel, dim3(xa_grid(H * B)), dim3(XA_THREADS), 0, st, q,
-                            static_cast<const __nv_bfloat16*>(s->cross_k) + l * ck_stride,
-                            static_cast<const __nv_bfloat16*>(s->cross_v) + l * cv_stride, T, w->kv_ld, d, H, H * B, att));
-    }
-    FusedProgram P = base;
-    tail_of(P, w->layers[c->n_layers - 1]);
-    {
-      FusedPhase ph = {};
-      ph.type = FZ_LAYERNORM;
-      ph.ln.x = x; ph.ln.w = w->ln_w; ph.ln.b = w->ln_b; ph.ln.y = xn;
-      P.ph[P.n_phases++] = ph;
-    }
-    if ((rc = dec_fused_segment(P, st))) return rc;
-  } else {
   for (int l = 0; l < c->n_layers; ++l) {
     const janus_dec_layer_t& L = w->layers[l];
     if ((rc = layernorm_bf16(x, L.ln1_w, L.ln1_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
     if ((rc = linear(xn, d, L.w_qkv, L.b_qkv, nullptr, qkv, B, 3 * d, ACT_NONE, 0, st, light))) return rc;
-    static int beam_sa = -1;   // JANUS_BEAM_SA=0: per-row kernel through the indirection instead of the shared-prefix one
-    if (beam_sa < 0) {
-      const char* e = getenv("JANUS_BEAM_SA");
-      beam_sa = e ? atoi(e) : 1;
-    }
+    // JANUS_OPT_BEAM_SHARED_SELF_ATTN = 0: per-row kernel through the indirection instead of the shared-prefix one
+    const int beam_sa = option(JANUS_OPT_BEAM_SHARED_SELF_ATTN, 1);
     bool sa_done = false;
     if (bm && beam_sa &&
         (rc = dec_self_attn_beam(qkv, static_cast<__nv_bfloat16*>(s->self_k) + l * self_stride,
@@ -1215,7 +1158,6 @@ static int32_t decode_step_impl(const janus_whisper_dims_t* c, const janus_decod
     if ((rc = linear(ff, 4 * d, L.w_fc2, L.b_fc2, x, x, B, d, ACT_NONE, 0, st, light))) return rc;
   }
   if ((rc = layernorm_bf16(x, w->ln_w, w->ln_b, xn, B, d, d, d, st, /*pdl=*/true))) return rc;
-  }
   if ((rc = linear(xn, d, w->tok_emb, nullptr, nullptr, s->logits, B, w->n_vocab_pad, ACT_NONE, 1, st, light))) return rc;
   if (bm) {
     BeamStepParams bp = {};

@@ -435,15 +435,21 @@ int make_tmap_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_t*
   return JANUS_OK;
 }
 
-static int g_num_sms = 0;
+// per-device caches: kernel attributes and the SM count belong to the CURRENT device (a process may drive several)
+int current_device_slot() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < 64 ? dev : 63;
+}
 int num_sms() {
-  if (!g_num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
+  static int n_sms[64] = {};
+  const int dev = current_device_slot();
+  if (!n_sms[dev]) {
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+    n_sms[dev] = v > 0 ? v : 148;
   }
-  return g_num_sms;
+  return n_sms[dev];
 }
 
 template <int BN>
@@ -451,10 +457,11 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams&
   using S = GemmSmem<BN>;
   p.n_tiles = p.N / BN;
   p.total_tiles = p.n_batch * p.m_tiles_per_batch * p.n_tiles;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {};
+  const int dev = current_device_slot();
+  if (!attr_set[dev]) {
     JANUS_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::BYTES));
-    attr_set = true;
+    attr_set[dev] = true;
   }
   const int grid = p.total_tiles < num_sms() ? p.total_tiles : num_sms();
   gemm_bf16_kernel<BN><<<grid, GEMM_THREADS, S::BYTES, stream>>>(ta, tb, p);

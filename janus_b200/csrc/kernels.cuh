@@ -61,45 +61,5 @@ int dec_beam_finalize(const int32_t* tokens, const int32_t* pos, int max_len, in
                       const janus_beam_state_t& bm, int32_t* best_tokens, float* best_score, int32_t* best_len,
                       cudaStream_t stream);
 
-// ---- fused decode segment (dec_fused.cu) -------------------------------------------------------
-enum FusedPhaseType { FZ_LINEAR = 0, FZ_SELF_ATTN = 1, FZ_LAYERNORM = 2 };
-
-struct FusedLinear {          // out[r, n] = act( LN?(A)[r, :] . W[n, :] + bias[n] ) (+ residual[r, n]); all bf16 but bias
-  const void* A;              // [rows, K], leading dimension lda
-  const float* ln_w;          // non-null: LayerNorm over the K (= d) features of every A row, fused into the load
-  const float* ln_b;
-  const void* W;              // [N, K]
-  const float* bias;          // [N] or null
-  const void* residual;       // [rows, N] or null (may alias out)
-  void* out;                  // [rows, N]
-  int lda, N, K, kc;          // kc: K chunk staged in shared memory (= d)
-  int act, cfg;               // cfg 0/1/2 -> 32/64/128 output columns per tile
-};
-struct FusedSelfAttn {        // KV-cache append + causal attention for every (stream, head)
-  const void* qkv;            // [rows, 3d]
-  void* k_cache;              // [rows, H, n_ctx, 64]
-  void* v_cache;
-  void* out;                  // [rows, d]
-  int n_ctx;
-};
-struct FusedLayerNorm {
-  const void* x; const float* w; const float* b; void* y;
-};
-struct FusedPhase {
-  int type;
-  FusedLinear lin;
-  FusedSelfAttn sa;
-  FusedLayerNorm ln;
-};
-constexpr int FZ_MAX_PHASES = 8;
-struct FusedProgram {
-  int n_phases, rows, d, n_heads;
-  const int32_t* pos;               // device scalar: current position
-  unsigned long long* barrier;      // device counter owned by the decode session (never reset)
-  FusedPhase ph[FZ_MAX_PHASES];
-};
-// Launches the persistent segment kernel (grid = number of SMs, all CTAs co-resident).
-int dec_fused_segment(const FusedProgram& prog, cudaStream_t stream);
-size_t dec_fused_smem_bytes(int d);
 
 }  // namespace janus

@@ -79,15 +79,3 @@ extern "C" int32_t janus_layernorm_bf16(const void* x, const float* w, const flo
   return janus::layernorm_bf16(static_cast<const __nv_bfloat16*>(x), w, b, static_cast<__nv_bfloat16*>(y), rows, d, d,
                                d, (cudaStream_t)stream);
 }
-
-// Diagnostic (not part of the product path): n dependent LayerNorm launches issued from C, for measuring
-// the dependent-launch latency of the decode chain with and without PDL (scripts/gpu_dec_bench2.py).
-extern "C" int32_t janus_debug_ln_chain(const void* x, const float* w, const float* b, void* y, int64_t rows,
-                                        int32_t d, int32_t n, void* stream) {
-  for (int i = 0; i < n; ++i) {
-    int rc = janus::layernorm_bf16(static_cast<const __nv_bfloat16*>(x), w, b, static_cast<__nv_bfloat16*>(y), rows, d,
-                                   d, d, (cudaStream_t)stream, true);
-    if (rc) return rc;
-  }
-  return JANUS_OK;
-}

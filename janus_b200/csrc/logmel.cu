@@ -69,7 +69,7 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
                      const int64_t* __restrict__ lengths, int decim, int n_mels,
                      const int32_t* __restrict__ mel_start, const int32_t* __restrict__ mel_len,
                      const float* __restrict__ mel_w, int mel_max_len, float* __restrict__ scratch,
-                     int* __restrict__ maxbuf, int nf_alloc) {
+                     int* __restrict__ maxbuf, int nf_alloc, int nf_cap) {
   extern __shared__ __align__(16) float lm_smem[];
   float2* s_w20 = reinterpret_cast<float2*>(lm_smem);           // 20
   float2* s_w400 = s_w20 + 20;                                   // 400
@@ -89,7 +89,7 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
   const int64_t len = (lengths[b] + decim - 1) / decim;  // samples after x[::decim]
   const int64_t L = len + LM_TAIL_PAD;
   int64_t nf = L / LM_HOP;                                // frames kept (last STFT frame dropped)
-  if (nf > LM_FRAMES + 1) nf = LM_FRAMES + 1;
+  if (nf > nf_cap) nf = nf_cap;
   const int t = blockIdx.x * LM_WARPS + warp;
   if (t >= nf) return;
 
@@ -156,22 +156,28 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
   if (lane == 0) atomicMax(maxbuf + b, float_key(mx));
 }
 
+// Window w = frames [seek, seek + 3000) of utterance u = win_utt[w] (win_utt == NULL: u = w, seek = 0): the slice +
+// pad_or_trim of faster-whisper's transcribe() loop, with the clamp floor of the WHOLE utterance.
 __global__ void logmel_finalize_kernel(const float* __restrict__ scratch, const int* __restrict__ maxbuf,
                                        const int64_t* __restrict__ lengths, int decim, int n_mels, int nf_alloc,
+                                       int nf_cap, const int32_t* __restrict__ win_utt,
+                                       const int32_t* __restrict__ win_seek,
                                        __nv_bfloat16* __restrict__ out_bf16, float* __restrict__ out_f32) {
   const int b = blockIdx.y;
-  const int64_t len = (lengths[b] + decim - 1) / decim;
+  const int u = win_utt ? win_utt[b] : b;
+  const int seek = win_utt ? win_seek[b] : 0;
+  const int64_t len = (lengths[u] + decim - 1) / decim;
   int64_t nf = (len + LM_TAIL_PAD) / LM_HOP;
-  if (nf > LM_FRAMES + 1) nf = LM_FRAMES + 1;
-  const int seg = (int)min((int64_t)LM_FRAMES, nf - 1);  // content_frames of the first window
-  const float floor_v = key_float(maxbuf[b]) - 8.0f;
+  if (nf > nf_cap) nf = nf_cap;
+  const int seg = (int)max((int64_t)0, min((int64_t)LM_FRAMES, nf - 1 - seek));  // content frames of this window
+  const float floor_v = key_float(maxbuf[u]) - 8.0f;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // over (LM_FRAMES + 2) * n_mels, time-major
   if (idx >= (LM_FRAMES + 2) * n_mels) return;
   const int row = idx / n_mels, m = idx - row * n_mels;
   const int t = row - 1;
   float y = 0.f;
   if (t >= 0 && t < seg) {
-    const float v = scratch[((int64_t)b * nf_alloc + t) * n_mels + m];
+    const float v = scratch[((int64_t)u * nf_alloc + seek + t) * n_mels + m];
     y = (fmaxf(v, floor_v) + 4.0f) / 4.0f;
   }
   if (out_bf16) out_bf16[((int64_t)b * (LM_FRAMES + 2) + row) * n_mels + m] = __float2bfloat16_rn(y);
@@ -184,32 +190,68 @@ using namespace janus;
 
 extern "C" int32_t janus_logmel_frames_alloc(void) { return LM_FRAMES + 1; }
 
-extern "C" int32_t janus_logmel_f32(const float* pcm, const int64_t* offsets, const int64_t* lengths, int32_t n,
-                                    int32_t decim, int32_t n_mels, const int32_t* mel_start,
-                                    const int32_t* mel_len, const float* mel_w, int32_t mel_max_len,
-                                    float* scratch, int32_t* maxbuf, void* mel_bf16_out, float* mel_f32_out,
-                                    void* stream) {
-  if (n <= 0) return JANUS_OK;
+static int32_t logmel_frames(const float* pcm, const int64_t* offsets, const int64_t* lengths, int32_t n, int32_t decim,
+                             int32_t n_mels, const int32_t* mel_start, const int32_t* mel_len, const float* mel_w,
+                             int32_t mel_max_len, float* scratch, int32_t* maxbuf, int32_t nf_alloc, cudaStream_t st) {
   JANUS_CHECK_ARG(pcm && offsets && lengths && mel_start && mel_len && mel_w && scratch && maxbuf, "logmel: null pointer");
-  JANUS_CHECK_ARG(mel_bf16_out || mel_f32_out, "logmel: no output requested");
   JANUS_CHECK_ARG(decim >= 1 && n_mels > 0 && n_mels <= 128 && mel_max_len > 0 && mel_max_len <= 64,
                   "logmel: unsupported decim/n_mels/mel_max_len");
+  JANUS_CHECK_ARG(nf_alloc >= 1, "logmel: nf_alloc must be >= 1");
   int rc = init_tables();
   if (rc) return rc;
-  cudaStream_t st = (cudaStream_t)stream;
-  const int nf_alloc = LM_FRAMES + 1;
   JANUS_CUDA(cudaMemsetAsync(maxbuf, 0x80, sizeof(int32_t) * n, st));
   const size_t smem = sizeof(float2) * 420 + sizeof(float) * 400 + sizeof(float) * n_mels * mel_max_len +
                       sizeof(int) * 2 * n_mels + sizeof(float) * LM_WARPS * (400 + 800 + 208);
   JANUS_CUDA(cudaFuncSetAttribute(logmel_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const dim3 grid((nf_alloc + LM_WARPS - 1) / LM_WARPS, n);
   logmel_frames_kernel<<<grid, LM_WARPS * 32, smem, st>>>(pcm, offsets, lengths, decim, n_mels, mel_start, mel_len,
-                                                          mel_w, mel_max_len, scratch, maxbuf, nf_alloc);
+                                                          mel_w, mel_max_len, scratch, maxbuf, nf_alloc, nf_alloc);
   JANUS_LAUNCH_CHECK("logmel_frames_kernel");
+  return JANUS_OK;
+}
+
+extern "C" int32_t janus_logmel_f32(const float* pcm, const int64_t* offsets, const int64_t* lengths, int32_t n,
+                                    int32_t decim, int32_t n_mels, const int32_t* mel_start,
+                                    const int32_t* mel_len, const float* mel_w, int32_t mel_max_len,
+                                    float* scratch, int32_t* maxbuf, void* mel_bf16_out, float* mel_f32_out,
+                                    void* stream) {
+  if (n <= 0) return JANUS_OK;
+  JANUS_CHECK_ARG(mel_bf16_out || mel_f32_out, "logmel: no output requested");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nf_alloc = LM_FRAMES + 1;
+  int rc = logmel_frames(pcm, offsets, lengths, n, decim, n_mels, mel_start, mel_len, mel_w, mel_max_len, scratch,
+                         maxbuf, nf_alloc, st);
+  if (rc) return rc;
   const int total = (LM_FRAMES + 2) * n_mels;
   const dim3 grid2((total + 255) / 256, n);
-  logmel_finalize_kernel<<<grid2, 256, 0, st>>>(scratch, maxbuf, lengths, decim, n_mels, nf_alloc,
-                                                static_cast<__nv_bfloat16*>(mel_bf16_out), mel_f32_out);
+  logmel_finalize_kernel<<<grid2, 256, 0, st>>>(scratch, maxbuf, lengths, decim, n_mels, nf_alloc, nf_alloc, nullptr,
+                                                nullptr, static_cast<__nv_bfloat16*>(mel_bf16_out), mel_f32_out);
+  JANUS_LAUNCH_CHECK("logmel_finalize_kernel");
+  return JANUS_OK;
+}
+
+extern "C" int32_t janus_logmel_utterance_f32(const float* pcm, const int64_t* offsets, const int64_t* lengths,
+                                              int32_t n, int32_t decim, int32_t n_mels, const int32_t* mel_start,
+                                              const int32_t* mel_len, const float* mel_w, int32_t mel_max_len,
+                                              float* scratch, int32_t nf_alloc, int32_t* maxbuf, void* stream) {
+  if (n <= 0) return JANUS_OK;
+  return logmel_frames(pcm, offsets, lengths, n, decim, n_mels, mel_start, mel_len, mel_w, mel_max_len, scratch,
+                       maxbuf, nf_alloc, (cudaStream_t)stream);
+}
+
+extern "C" int32_t janus_logmel_windows_f32(const float* scratch, const int32_t* maxbuf, const int64_t* lengths,
+                                            int32_t decim, int32_t n_mels, int32_t nf_alloc, const int32_t* win_utt,
+                                            const int32_t* win_seek, int32_t n_windows, void* mel_bf16_out,
+                                            float* mel_f32_out, void* stream) {
+  if (n_windows <= 0) return JANUS_OK;
+  JANUS_CHECK_ARG(scratch && maxbuf && lengths && win_utt && win_seek, "logmel_windows: null pointer");
+  JANUS_CHECK_ARG(mel_bf16_out || mel_f32_out, "logmel_windows: no output requested");
+  JANUS_CHECK_ARG(decim >= 1 && n_mels > 0 && n_mels <= 128 && nf_alloc >= 1, "logmel_windows: bad arguments");
+  const int total = (LM_FRAMES + 2) * n_mels;
+  const dim3 grid2((total + 255) / 256, n_windows);
+  logmel_finalize_kernel<<<grid2, 256, 0, (cudaStream_t)stream>>>(
+      scratch, maxbuf, lengths, decim, n_mels, nf_alloc, nf_alloc, win_utt, win_seek,
+      static_cast<__nv_bfloat16*>(mel_bf16_out), mel_f32_out);
   JANUS_LAUNCH_CHECK("logmel_finalize_kernel");
   return JANUS_OK;
 }

@@ -84,7 +84,7 @@ class _Lane:
         self.stream = torch.cuda.Stream(dev)
         with torch.cuda.stream(self.stream):
             self.session = DecodeSession(enc.whisper, enc.lane_batch, enc.max_new_tokens, light=enc.light,
-                                         steps_per_graph=enc.steps_per_graph, fused=enc.fused, latent=enc.latent,
+                                         steps_per_graph=enc.steps_per_graph, latent=enc.latent,
                                          beam=enc.beam)
             self.session._ensure_graph()
         self.stream.synchronize()
@@ -114,7 +114,7 @@ class SemanticEncoder:
                  device=None, seed: int = 0, weights: dict | None = None, weight_profile: str = "confident",
                  prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, lane_batch: int = 64,
                  n_lanes: int | None = None, steps_per_graph: int = 10, light: bool | None = None,
-                 fused: bool = False, enc_chunk: int = 64, latent: bool | None = None, beam: int = 0) -> None:
+                 enc_chunk: int = 64, latent: bool | None = None, beam: int = 0) -> None:
         self.dims = PRESETS[model] if isinstance(model, str) else model
         self.spec = tokenizer_spec(self.dims)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -128,14 +128,13 @@ class SemanticEncoder:
         self.n_lanes = n_lanes if n_lanes is not None else 2 * self.lanes_per_call
         if self.n_lanes < self.lanes_per_call:
             raise ValueError("n_lanes must be >= batch / lane_batch")
-        self.fused = fused
         # 0: greedy (what the reference calls: beam_size=1, transcriber.py:55); >= 1: beam search with that many beams
         # per window (BASELINE configs[3] uses 5), decode rows = lane_batch * beam
         self.beam = beam
         # None: decode sessions pick latent cross-attention (over the encoder states, half the HBM bytes per
         # step) whenever the model fits and a lane holds >= DecodeSession.LATENT_MIN_BATCH windows
         self.latent = latent
-        self.light = (self.lane_batch <= 64 and not fused and not latent and not beam) if light is None else light
+        self.light = (self.lane_batch <= 64 and not latent and not beam) if light is None else light
         self.max_new_tokens, self.steps_per_graph = max_new_tokens, steps_per_graph
         self.decim = input_sample_rate // 16000
         assert input_sample_rate in (16000, 48000)
@@ -244,10 +243,6 @@ class SemanticEncoder:
                 lane.ready.record(self.enc_stream)
             with torch.cuda.stream(lane.stream):
                 lane.stream.wait_event(lane.ready)
-                if self.fused and self._last_decode is not None:
-                    # the fused segment kernels wait on each other across CTAs (grid barrier): keep at most one
-                    # decode chain in flight so that two chains can never hold partial sets of SMs
-                    lane.stream.wait_event(self._last_decode)
                 ses = lane.session
                 ses.reset()
                 ses.run_steps()

@@ -2,16 +2,34 @@
 :10-91): same constructor (`model_size='base.en'`), `transcribe_buffer(audio_buffer) -> str` with the
 same coercions, the same `[::3]` 48 kHz -> 16 kHz decimation (fused into the log-mel kernel's loads),
 greedy decode (beam_size=1, language 'en'), and the same `' '.join(seg.text.strip()).strip()` assembly.
+
+Around the model, the utterance-level loop of `WhisperModel.transcribe` (faster-whisper, RECALLED: SURVEY.md 3.5;
+restated for the tests in oracle/transcribe_ref.py) is reproduced with its defaults, which are what the reference
+gets because it passes none of these arguments (transcriber.py:53-57):
+  * features are computed ONCE per utterance (one global max-8 clamp, continuous STFT) and 3000-frame windows are
+    sliced at `seek`, zero-padded in feature space;
+  * `seek` advances by the last timestamp the model emitted (a full window if the tokens end in a single timestamp or
+    hold no timestamp pair);
+  * `condition_on_previous_text=True`: windows after the first are prompted with <|startofprev|> + the last 223
+    tokens of the text so far;
+  * the no-speech gate: a window with no_speech_prob > 0.6 whose avg_logprob is not > -1.0 is skipped, so silence
+    returns '' and the caller sends no packet (/root/reference/backend/services/engine.py:536).
+Not reproduced: the temperature-fallback loop (re-decoding with SAMPLING at t = 0.2 ... 1.0 when avg_logprob < -1 or
+the compression ratio > 2.4): the t = 0 result is always accepted.
+
 `beam_size` is an optional extra constructor argument (default 1 = what the reference passes at :55); a value > 1
 decodes with that many beams per window (BASELINE configs[3]) through janus_whisper_decode_beam_step.
 
-The reference loads pretrained weights from the HF hub through faster-whisper; nothing is downloadable
-here, so by default the named architecture is randomly initialised from a fixed seed (set
-JANUS_B200_WHISPER_SEED / pass `weights=` to change that). Token ids are turned into text by the
-shared deterministic table in whisper/config.py because no Whisper vocabulary file exists offline.
+Weights: the reference's `WhisperModel(model_size)` resolves the name to a pretrained checkpoint in the Hugging Face
+cache. Here `model_path=` (or $JANUS_B200_WHISPER_PATH, or a checkpoint found in the local caches for that name) is
+loaded through `whisper.weights.load_weights`, with the tokenizer.json next to it (`tokenizer=`) turning ids into
+text. When nothing is found -- there is no network here -- the named architecture is randomly initialised from a
+fixed seed and a warning is logged; ids then map to the shared synthetic table of whisper/config.py.
 """
 from __future__ import annotations
 
+import glob
+import logging
 import os
 import threading
 import wave
@@ -19,71 +37,176 @@ import wave
 import numpy as np
 import torch
 
-from ..pipeline import join_segments, split_text_segments
-from ..whisper.config import PRESETS, tokenizer_spec
+from ..pipeline import join_segments
+from ..whisper.config import PRESETS, detokenize, tokenizer_spec
 from ..whisper.engine import DecodeSession, WhisperEngine
-from ..whisper.weights import init_random_weights
+from ..whisper.frontend import N_FRAMES
+from ..whisper.weights import init_random_weights, load_weights
 
-WINDOW_SAMPLES_16K = 480000   # 30 s
+logger = logging.getLogger(__name__)
+
 MAX_NEW_TOKENS = 448          # faster-whisper: max_length=448 (DecodeSession caps at 448 - len(prompt))
+_CAPTURE_LOCK = threading.Lock()   # CUDA-graph capture of any Transcriber in this process is serialised
+
+
+def find_pretrained(model_size: str) -> str | None:
+    """A local checkpoint for `model_size`, in the places the reference's stack would have put one:
+    $JANUS_B200_WHISPER_PATH, the HF cache (faster-whisper's CTranslate2 conversions `Systran/faster-whisper-<size>`,
+    then `openai/whisper-<size>`), openai-whisper's ~/.cache/whisper/<size>.pt. None if there is none."""
+    env = os.environ.get("JANUS_B200_WHISPER_PATH")
+    if env:
+        return env
+    hf = os.environ.get("HF_HOME", os.path.join(os.path.expanduser("~"), ".cache", "huggingface"))
+    for repo in (f"models--Systran--faster-whisper-{model_size}", f"models--openai--whisper-{model_size}"):
+        for snap in sorted(glob.glob(os.path.join(hf, "hub", repo, "snapshots", "*"))):
+            if any(os.path.exists(os.path.join(snap, f)) for f in ("model.bin", "model.safetensors", "pytorch_model.bin")):
+                return snap
+    pt = os.path.join(os.path.expanduser("~"), ".cache", "whisper", f"{model_size}.pt")
+    return pt if os.path.exists(pt) else None
 
 
 class Transcriber:
     def __init__(self, model_size: str = 'base.en', weights: dict | None = None, device=None,
-                 beam_size: int = 1) -> None:
+                 beam_size: int = 1, model_path: str | None = None, tokenizer: str | None = None) -> None:
         if not 1 <= beam_size <= 8:
             raise ValueError("beam_size must be in 1 .. 8")
         self.beam_size = beam_size
-        if model_size not in PRESETS:
-            raise ValueError(f"unknown Whisper model size {model_size!r}; known: {sorted(PRESETS)}")
-        self.dims = PRESETS[model_size]
-        self.spec = tokenizer_spec(self.dims)
+        # WhisperModel.transcribe() defaults (the reference overrides none of them)
+        self.condition_on_previous_text = True
+        self.no_speech_threshold = 0.6
+        self.log_prob_threshold = -1.0
+        self.max_windows: int | None = None   # safety valve for tests with random weights (faster-whisper has none)
+        self.pretrained = False
+        path = model_path if model_path is not None else (find_pretrained(model_size) if weights is None else None)
+        if weights is None and path is not None:
+            self.dims, weights = load_weights(path, name=model_size)
+            self.pretrained = True
+            if tokenizer is None:
+                cand = os.path.join(path if os.path.isdir(path) else os.path.dirname(path), "tokenizer.json")
+                tokenizer = cand if os.path.exists(cand) else None
+        else:
+            if model_size not in PRESETS:
+                raise ValueError(f"unknown Whisper model size {model_size!r}; known: {sorted(PRESETS)}")
+            self.dims = PRESETS[model_size]
+        if tokenizer is not None:
+            from ..whisper.tokenizer import WhisperTokenizer
+            self.spec = WhisperTokenizer.from_file(tokenizer, self.dims).spec()
+        else:
+            self.spec = tokenizer_spec(self.dims)
         if weights is None:
             seed = int(os.environ.get("JANUS_B200_WHISPER_SEED", "0"))
+            logger.warning("no pretrained Whisper checkpoint for %r found locally (set JANUS_B200_WHISPER_PATH or pass "
+                           "model_path=): using seeded random-init weights, text is synthetic", model_size)
             weights = init_random_weights(self.dims, seed=seed, profile="confident")
         self.model = WhisperEngine(self.dims, weights, device, self.spec)
-        self._sessions: dict[int, DecodeSession] = {}
+        self._sessions: dict[tuple, DecodeSession] = {}
         self._lock = threading.Lock()  # called from a 2-worker ThreadPoolExecutor in the reference
+        self.last_trace: list = []     # per window of the last call: seek, tokens, no_speech_prob, avg_logprob, skipped
+        self.last_segments: list = []  # per emitted segment of the last call: faster-whisper's Segment fields
+        # capture the single-window step graph now, not inside the first transcribe_buffer call on a worker thread
+        with self._lock, torch.cuda.device(self.model.device):
+            self._session(len(self.spec.sot_sequence), self.beam_size)
 
-    def _session(self, batch: int) -> DecodeSession:
-        s = self._sessions.get(batch)
+    def _session(self, n_prompt: int, beam_size: int) -> DecodeSession:
+        """One single-window session per prompt LENGTH (the length is baked into the step; the tokens are data).
+        The bare sot prompt replays a CUDA graph; conditioned prompts (windows after the first of a > 30 s utterance)
+        run the same kernels eagerly."""
+        key = (n_prompt, beam_size)
+        s = self._sessions.get(key)
         if s is None:
-            s = DecodeSession(self.model, batch, MAX_NEW_TOKENS, beam=self.beam_size if self.beam_size > 1 else 0)
-            self._sessions[batch] = s
+            n_sot = len(self.spec.sot_sequence)
+            base = n_prompt == n_sot
+            if len(self._sessions) >= 8 and not base:   # bound the cache: conditioned prompt lengths vary
+                for k in [k for k in self._sessions if k[0] != n_sot][:1]:
+                    del self._sessions[k]
+            prompt = [self.spec.sot_prev] * (n_prompt - n_sot) + list(self.spec.sot_sequence)
+            s = DecodeSession(self.model, 1, MAX_NEW_TOKENS, beam=beam_size if beam_size > 1 else 0,
+                              use_graph=base, prompt=prompt)
+            if base:
+                with _CAPTURE_LOCK:
+                    s._ensure_graph()
+            self._sessions[key] = s
         return s
 
-    def _transcribe(self, audio: np.ndarray, decim: int) -> str:
-        """audio: float32 at 16 kHz * decim. Windows of 30 s are decoded as one batch."""
+    # ---- one window ---------------------------------------------------------------------------
+    def _decode_window(self, enc: torch.Tensor, prompt: list[int], beam_size: int):
+        """-> (tokens before <|endoftext|>, sum_logprob, no_speech_prob)."""
+        ses = self._session(len(prompt), beam_size)
+        ses.set_prompt(prompt)
+        ses.cross_kv(enc)
+        ses.reset()
+        nsp = None
+        for step in range(ses.n_steps):   # stop as soon as the window has emitted <|endoftext|>
+            if ses.graph is not None:
+                ses.graph.replay()
+            else:
+                ses._step()
+            if step == ses.sot_index:
+                nsp = ses.no_speech_prob()
+            if step % 8 == 7 and step >= ses.n_prompt and int(ses.n_done.item()) >= 1:
+                break
+        if ses.beam:
+            tok, lp = ses.finalize()
+            row, sum_lp = tok[0].cpu().tolist(), float(lp[0])
+        else:
+            row, sum_lp = ses.tokens[0, ses.n_prompt:].cpu().tolist(), float(ses.sum_logprob[0])
+        eot = self.spec.eot
+        tokens = row[:row.index(eot)] if eot in row else row
+        return tokens, sum_lp, float(nsp[0]) if nsp is not None else 0.0
+
+    # ---- the utterance loop -------------------------------------------------------------------
+    def _transcribe(self, audio: np.ndarray, decim: int, beam_size: int | None = None,
+                    condition_on_previous_text: bool | None = None) -> str:
+        """audio: float32 at 16 kHz * decim (the kernel reads audio[::decim])."""
+        beam_size = self.beam_size if beam_size is None else beam_size
+        if not 1 <= beam_size <= 8:
+            raise ValueError("beam_size must be in 1 .. 8")
+        cond = self.condition_on_previous_text if condition_on_previous_text is None else condition_on_previous_text
+        self.last_trace, self.last_segments = [], []
         if audio.size == 0:
             return ''
-        win = WINDOW_SAMPLES_16K * decim
-        windows = [audio[i:i + win] for i in range(0, len(audio), win)]
-        dev = self.model.device
+        spec, fe, dev = self.spec, self.model.frontend, self.model.device
+        tb, eot = spec.timestamp_begin, spec.eot
+        n_frames = fe.n_frames(len(audio), decim)
+        content_frames = n_frames - 1
+        texts: list[str] = []
+        trace: list = []
+        segments: list = []
         with self._lock, torch.cuda.device(dev):
-            lens = torch.tensor([len(w) for w in windows], dtype=torch.int64)
-            offs = torch.cumsum(lens, 0) - lens
             pcm = torch.from_numpy(np.ascontiguousarray(audio)).to(dev)
-            mel_pad, _ = self.model.frontend(pcm, offs.to(dev), lens.to(dev), decim=decim)
-            enc = self.model.encode(mel_pad)
-            ses = self._session(len(windows))
-            ses._ensure_graph()
-            ses.cross_kv(enc)
-            ses.reset()
-            done = 0
-            for step in range(ses.n_steps):   # stop as soon as every window has emitted <|endoftext|>
-                if ses.graph is not None:
-                    ses.graph.replay()
-                else:
-                    ses._step()
-                if step % 8 == 7:
-                    done = int(ses.n_done.item())
-                    if done >= len(windows):
-                        break
-            tokens = (ses.finalize()[0] if ses.beam else ses.tokens[:, ses.n_prompt:]).cpu().numpy()
-        text_parts = []
-        for row in tokens:
-            text_parts.extend(split_text_segments(row, self.spec))
-        return join_segments(text_parts)
+            offs = torch.zeros(1, dtype=torch.int64, device=dev)
+            lens = torch.tensor([len(audio)], dtype=torch.int64, device=dev)
+            scratch, maxbuf = fe.utterance(pcm, offs, lens, max(n_frames, 1), decim)
+            seek, all_tokens = 0, []
+            while seek < content_frames and (self.max_windows is None or len(trace) < self.max_windows):
+                segment_size = min(N_FRAMES, content_frames - seek)
+                mel_pad, _ = fe.windows(scratch, maxbuf, lens, [0], [seek], decim)
+                enc = self.model.encode(mel_pad)
+                prompt = list(spec.sot_sequence)
+                if cond and all_tokens:
+                    prompt = [spec.sot_prev] + all_tokens[-(spec.max_length // 2 - 1):] + prompt
+                tokens, sum_lp, nsp = self._decode_window(enc, prompt, beam_size)
+                avg_logprob = sum_lp / (len(tokens) + 1)
+                skip = nsp > self.no_speech_threshold and not avg_logprob > self.log_prob_threshold
+                trace.append({"seek": seek, "tokens": tokens, "no_speech_prob": nsp, "avg_logprob": avg_logprob,
+                              "skipped": skip, "n_prompt": len(prompt)})
+                if skip:
+                    seek += segment_size
+                    continue
+                segs, advance = split_window_segments(tokens, tb, segment_size)
+                t0 = seek * 0.01                      # time_offset: 10 ms per feature frame
+                for start, end, sl in segs:
+                    text = detokenize([t for t in sl if t < eot], spec)
+                    if start == end or not text.strip():
+                        continue
+                    texts.append(text)
+                    segments.append({"id": len(segments) + 1, "seek": seek, "start": t0 + 0.02 * start,
+                                     "end": t0 + 0.02 * end, "text": text, "tokens": sl, "avg_logprob": avg_logprob,
+                                     "no_speech_prob": nsp, "temperature": 0.0})
+                seek += advance
+                all_tokens.extend(tokens)
+        self.last_trace, self.last_segments = trace, segments
+        return join_segments(texts)
 
     def transcribe_buffer(self, audio_buffer) -> str:
         if isinstance(audio_buffer, list):                      # transcriber.py:42-43
@@ -115,3 +238,27 @@ class Transcriber:
         if sr % 16000 != 0:
             raise ValueError(f"unsupported WAV sample rate {sr} (need a multiple of 16 kHz)")
         return self._transcribe(x, decim=sr // 16000)
+
+
+def split_window_segments(tokens: list[int], timestamp_begin: int, segment_size: int):
+    """One window's tokens (before <|endoftext|>) -> ([(start_pos, end_pos, tokens)], frames to advance `seek` by),
+    the segment / seek rule of faster-whisper's generate_segments (timestamp positions are 0.02 s = 2 feature
+    frames): split after every CONSECUTIVE timestamp pair; with at least one pair the window ends at the last pair
+    unless the tokens end in a single timestamp; with none the whole list is one segment and the window is consumed."""
+    tb = timestamp_begin
+    is_ts = [t >= tb for t in tokens]
+    single_ending = len(tokens) >= 2 and not is_ts[-2] and is_ts[-1]
+    cuts = [i for i in range(1, len(tokens)) if is_ts[i] and is_ts[i - 1]]
+    segs = []
+    if cuts:
+        if single_ending:
+            cuts = cuts + [len(tokens)]
+        last = 0
+        for cur in cuts:
+            sl = tokens[last:cur]
+            segs.append((sl[0] - tb, sl[-1] - tb, sl))
+            last = cur
+        return segs, (segment_size if single_ending else (tokens[last - 1] - tb) * 2)
+    stamps = [t for t in tokens if t >= tb]
+    end = stamps[-1] - tb if stamps and stamps[-1] != tb else segment_size // 2
+    return [(0, end, tokens)], segment_size

@@ -90,6 +90,9 @@ class TokenizerSpec:
     non_speech: tuple = ()
     max_initial_timestamp_index: int = 50
     max_length: int = 448
+    # id -> text for the text tokens of one segment (a real vocabulary: whisper/tokenizer.py); None = the shared
+    # synthetic table below (no Whisper vocabulary exists offline)
+    decoder: object = field(default=None, compare=False, repr=False)
 
     @property
     def sot_sequence(self) -> tuple:
@@ -123,7 +126,10 @@ def tokenizer_spec(dims: WhisperDims) -> TokenizerSpec:
 def detokenize(ids, spec: TokenizerSpec) -> str:
     """Shared deterministic id -> string table. No Whisper vocabulary exists offline (SURVEY.md
     section 3.5), so text tokens map to a fixed synthetic word list; special/timestamp tokens map
-    to nothing, exactly as a real tokenizer's decode() drops them."""
+    to nothing, exactly as a real tokenizer's decode() drops them. With a real vocabulary loaded
+    (`spec.decoder`, whisper/tokenizer.py) that tokenizer's own decode is used instead."""
+    if spec.decoder is not None:
+        return spec.decoder(ids)
     words = []
     for t in ids:
         t = int(t)

@@ -127,7 +127,7 @@ class DecodeStateStruct(C.Structure):
                 ("self_ld", C.c_int32), ("reserved0", C.c_int32)] + \
                [(n, C.c_void_p) for n in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done",
                                           "n_done", "self_k", "self_v", "cross_k", "cross_v", "x", "xn", "qkv",
-                                          "att", "q", "ff", "logits", "barrier", "enc_out", "qlat", "zlat")]
+                                          "att", "q", "ff", "logits", "reserved1", "enc_out", "qlat", "zlat")]
 
 
 class BeamStateStruct(C.Structure):
@@ -198,19 +198,19 @@ class DecodeSession:
     (row = window * beam + k); cross-attention inputs exist once per window."""
 
     DECODE_LIGHT = 1   # JANUS_DECODE_LIGHT
-    DECODE_FUSED = 2   # JANUS_DECODE_FUSED
     DECODE_LATENT = 4  # JANUS_DECODE_LATENT
     DECODE_KV_SWAPPED = 8  # JANUS_DECODE_KV_SWAPPED
     LATENT_MIN_BATCH = 128   # the latent kernel runs one CTA per window: below ~one window per SM the K/V kernel
                              # (one CTA per window and head) fills the machine better
 
     def __init__(self, engine: WhisperEngine, batch: int, max_new_tokens: int, use_graph: bool = True,
-                 light: bool = False, steps_per_graph: int = 1, fused: bool = False,
-                 latent: bool | None = None, beam: int = 0, patience: float = 1.0) -> None:
+                 light: bool = False, steps_per_graph: int = 1,
+                 latent: bool | None = None, beam: int = 0, patience: float = 1.0,
+                 prompt: tuple | list | None = None) -> None:
         if not hasattr(engine, "dec_weights"):
             raise RuntimeError("engine was built without decoder weights")
-        if beam and (light or fused):
-            raise ValueError("beam search excludes light / fused decode sessions")
+        if beam and light:
+            raise ValueError("beam search excludes light decode sessions")
         if not 0 <= beam <= 8:
             raise ValueError("beam must be in 0 .. 8 (JANUS_MAX_BEAM)")
         self.eng, self.B = engine, batch
@@ -218,7 +218,13 @@ class DecodeSession:
         NW = batch                 # windows: cross-attention inputs, results
         batch = batch * max(beam, 1)   # decode rows
         d, spec, dev = engine.dims, engine.spec, engine.device
-        self.n_prompt = len(spec.sot_sequence)
+        # `prompt`: the whole forced prefix, e.g. [<|startofprev|>, previous text ..., <|startoftranscript|>, ...]
+        # (faster-whisper's condition_on_previous_text); default: the sot sequence alone
+        prompt = tuple(int(t) for t in (prompt if prompt is not None else spec.sot_sequence))
+        if len(prompt) >= spec.max_length:
+            raise ValueError("prompt leaves no room for new tokens")
+        self.n_prompt = len(prompt)
+        self.sot_index = max(i for i, t in enumerate(prompt) if t == spec.sot) if spec.sot in prompt else 0
         self.max_new = min(max_new_tokens, spec.max_length - self.n_prompt)
         self.max_len = self.n_prompt + self.max_new
         n, L, H = d.n_text_state, d.n_text_layer, d.n_text_head
@@ -239,11 +245,11 @@ class DecodeSession:
         if latent is None:
             # beam search defaults to the K/V-cache form: its kernel serves all beams of a window from ONE pass over
             # K / V (4.6 MB per window and layer), while the latent kernel walks the encoder states once per beam
-            latent = engine.latent_ok and not light and not fused and NW >= self.LATENT_MIN_BATCH and beam <= 1
+            latent = engine.latent_ok and not light and NW >= self.LATENT_MIN_BATCH and beam <= 1
         if latent and not engine.latent_ok:
             raise ValueError("latent cross-attention needs d % 128 == 0, d <= 1024 and <= 16 heads")
-        if latent and (light or fused):
-            raise ValueError("latent cross-attention excludes light / fused decode sessions")
+        if latent and light:
+            raise ValueError("latent cross-attention excludes light decode sessions")
         self.latent = latent
         if latent:
             # cross-attention over the encoder states themselves: no per-layer K/V (2 * L times smaller)
@@ -263,17 +269,14 @@ class DecodeSession:
         self.qkv, self.att = torch.zeros((B, 3 * n), **bf), torch.zeros((B, n), **bf)
         self.q, self.ff = torch.zeros((B, n), **bf), torch.zeros((B, 4 * n), **bf)
         self.logits = torch.zeros((B, engine.n_vocab_pad), dtype=torch.float32, device=dev)
-        self.prompt = torch.tensor(list(spec.sot_sequence), **i32)
+        self.prompt = torch.tensor(list(prompt), **i32)
         s = DecodeStateStruct()
         s.batch, s.max_len, s.n_prompt = B, self.max_len, self.n_prompt
         s.self_ld = self.self_ld
         if light and B > 64:
             raise ValueError("light decode sessions hold at most 64 streams")
-        s.flags = (self.DECODE_LIGHT if light else 0) | (self.DECODE_FUSED if fused else 0) | \
+        s.flags = (self.DECODE_LIGHT if light else 0) | \
                   (self.DECODE_LATENT if latent else 0) | (self.DECODE_KV_SWAPPED if beam and not latent else 0)
-        self.barrier = torch.zeros(2, dtype=torch.int64, device=dev)   # grid-barrier counter of the fused path
-        s.barrier = self.barrier.data_ptr()
-        self.fused = fused
         for name in ("tokens", "forced", "choice", "logprob", "sum_logprob", "pos", "done", "n_done", "self_k",
                      "self_v", "x", "xn", "qkv", "att", "q", "ff", "logits"):
             setattr(s, name, getattr(self, name).data_ptr())
@@ -317,9 +320,8 @@ class DecodeSession:
         # several steps per captured graph: fewer host launches per lane when many lanes are in flight
         self.steps_per_graph = max(1, min(steps_per_graph, self.n_steps))
         self.tail_graph: torch.cuda.CUDAGraph | None = None
-        # embed, final LN, logits, pick, advance + 11 per layer; fused: embed, (segment + cross-attn) per layer,
-        # final segment, logits, pick, advance
-        self.kernels_per_step = (1 + 2 * L + 1 + 3) if fused else (3 + (13 if latent else 11) * L + 2 + 1)
+        # embed, final LN, logits, pick, advance + 11 (13 with latent cross-attention) per layer
+        self.kernels_per_step = 3 + (13 if latent else 11) * L + 2 + 1
         if beam:
             self.kernels_per_step += 1   # candidates + update instead of pick
 
@@ -331,6 +333,23 @@ class DecodeSession:
             return
         _abi.call("janus_whisper_decode_step", C.byref(e.c_dec_dims), C.byref(e.dec_weights), C.byref(self.state),
                   torch.cuda.current_stream(e.device).cuda_stream)
+
+    def set_prompt(self, prompt) -> None:
+        """Replaces the forced prefix by another one of the SAME length (the length is baked into the captured
+        step; the tokens are data)."""
+        prompt = [int(t) for t in prompt]
+        if len(prompt) != self.n_prompt:
+            raise ValueError("set_prompt: the prompt length is fixed per session")
+        spec = self.eng.spec
+        self.prompt.copy_(torch.tensor(prompt, dtype=torch.int32))
+        self.sot_index = max(i for i, t in enumerate(prompt) if t == spec.sot) if spec.sot in prompt else 0
+
+    def no_speech_prob(self) -> torch.Tensor:
+        """softmax(logits)[<|nospeech|>] per row, fp32 device tensor. Only meaningful right after the step that
+        consumed <|startoftranscript|> (step index `sot_index`): that is the distribution faster-whisper /
+        CTranslate2 report as `no_speech_prob` (return_no_speech_prob=True)."""
+        V = self.eng.dims.n_vocab
+        return torch.softmax(self.logits[:, :V], dim=-1)[:, self.eng.spec.no_speech].clone()
 
     def finalize(self):
         """Beam search: ranks every window's finished / live hypotheses (score / n_tokens) into best_tokens /
@@ -384,14 +403,16 @@ class DecodeSession:
         self._step()  # eager warm-up: sets kernel attributes outside capture
         torch.cuda.current_stream(self.eng.device).synchronize()
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        # thread_local: another service thread (the reference runs STT and prosody from a 2-worker pool) may call
+        # cudaMalloc / pin memory while this thread captures
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
             for _ in range(self.steps_per_graph):
                 self._step()
         self.graph = g
         rem = self.n_steps % self.steps_per_graph
         if rem:
             t = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(t):
+            with torch.cuda.graph(t, capture_error_mode="thread_local"):
                 for _ in range(rem):
                     self._step()
             self.tail_graph = t

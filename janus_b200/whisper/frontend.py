@@ -72,3 +72,35 @@ class LogMelFrontend:
                   scratch.data_ptr(), maxbuf.data_ptr(), out_bf16.data_ptr() if want_bf16 else None,
                   out_f32.data_ptr() if want_f32 else None, torch.cuda.current_stream(dev).cuda_stream)
         return (out_bf16 if want_bf16 else None), out_f32
+
+    # ---- utterances longer than one window ------------------------------------------------------
+    @staticmethod
+    def n_frames(n_samples: int, decim: int = 1) -> int:
+        """Feature frames faster-whisper keeps for an utterance of n_samples source-rate samples
+        (+160 zero samples, centred STFT at hop 160, last frame dropped); content_frames = n_frames - 1."""
+        return (-(-n_samples // decim) + 160) // HOP
+
+    def utterance(self, pcm: torch.Tensor, offsets: torch.Tensor, lengths: torch.Tensor, nf_alloc: int, decim: int = 1):
+        """Pass 1 over whole utterances: (scratch fp32 [n, nf_alloc, n_mels] log10-mel, maxbuf int32 [n])."""
+        n, dev = int(offsets.numel()), self.device
+        scratch = torch.empty((n, nf_alloc, self.n_mels), dtype=torch.float32, device=dev)
+        maxbuf = torch.empty(n, dtype=torch.int32, device=dev)
+        _abi.call("janus_logmel_utterance_f32", pcm.data_ptr(), offsets.data_ptr(), lengths.data_ptr(), n, decim,
+                  self.n_mels, self.mel_start.data_ptr(), self.mel_len.data_ptr(), self.mel_w.data_ptr(), self.max_len,
+                  scratch.data_ptr(), nf_alloc, maxbuf.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+        return scratch, maxbuf
+
+    def windows(self, scratch: torch.Tensor, maxbuf: torch.Tensor, lengths: torch.Tensor, win_utt, win_seek,
+                decim: int = 1, want_f32: bool = False):
+        """Pass 2: window w = frames [win_seek[w], +3000) of utterance win_utt[w], clamped with that utterance's
+        global max - 8 and zero-padded in feature space. Returns (mel_pad bf16 [n_w, 3002, n_mels], fp32 | None)."""
+        dev = self.device
+        wu = torch.as_tensor(win_utt, dtype=torch.int32).to(dev)
+        ws = torch.as_tensor(win_seek, dtype=torch.int32).to(dev)
+        nw = int(wu.numel())
+        out_bf16 = torch.empty((nw, N_FRAMES + 2, self.n_mels), dtype=torch.bfloat16, device=dev)
+        out_f32 = torch.empty((nw, self.n_mels, N_FRAMES), dtype=torch.float32, device=dev) if want_f32 else None
+        _abi.call("janus_logmel_windows_f32", scratch.data_ptr(), maxbuf.data_ptr(), lengths.data_ptr(), decim,
+                  self.n_mels, scratch.shape[1], wu.data_ptr(), ws.data_ptr(), nw, out_bf16.data_ptr(),
+                  out_f32.data_ptr() if want_f32 else None, torch.cuda.current_stream(dev).cuda_stream)
+        return out_bf16, out_f32

@@ -187,20 +187,27 @@ def suppress_mask_for(spec: TokenizerSpec) -> torch.Tensor:
 
 
 def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor, max_new_tokens: int,
-                  stop_at_eot: bool = True, return_margins: bool = False, vectorized: bool = False):
+                  stop_at_eot: bool = True, return_margins: bool = False, vectorized: bool = False,
+                  prompt: list | None = None, return_no_speech: bool = False):
     """Batched greedy decode at temperature 0. Returns tokens [B, max_new_tokens] (eot-padded after
     the first eot), sum of log-probs [B], and optionally the top-1/top-2 margin at every step."""
     B = enc_out.shape[0]
     st = DecoderState(W, dims, enc_out)
     sup = suppress_mask_for(spec)
-    prompt = torch.tensor([list(spec.sot_sequence)] * B, dtype=torch.long)
-    logits = st.step(prompt)[:, -1]
+    # `prompt`: the forced prefix of every row (default: the sot sequence); with previous-text conditioning it is
+    # [<|startofprev|>, previous tokens ..., <|startoftranscript|>, ...]. no_speech_prob = softmax of the logits at the
+    # <|startoftranscript|> position (faster-whisper return_no_speech_prob / openai-whisper DecodingTask._main_loop)
+    plist = list(prompt) if prompt is not None else list(spec.sot_sequence)
+    all_logits = st.step(torch.tensor([plist] * B, dtype=torch.long))
+    logits = all_logits[:, -1]
+    sot_index = max(i for i, t in enumerate(plist) if t == spec.sot) if spec.sot in plist else 0
+    no_speech = torch.softmax(all_logits[:, sot_index].float(), dim=-1)[:, spec.no_speech]
     gen = [[] for _ in range(B)]
     done = [False] * B
     out = torch.full((B, max_new_tokens), spec.eot, dtype=torch.long)
     sum_lp = torch.zeros(B)
     margins = torch.full((B, max_new_tokens), float("inf"))
-    n_steps = min(max_new_tokens, spec.max_length - len(spec.sot_sequence))
+    n_steps = min(max_new_tokens, spec.max_length - len(plist))
     for t in range(n_steps):
         nxt = torch.full((B,), spec.eot, dtype=torch.long)
         if vectorized:   # the same rules for all rows at once (apply_logit_rules_batch)
@@ -222,9 +229,8 @@ def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tens
         if all(done) or t == n_steps - 1:
             break
         logits = st.step(nxt[:, None])[:, -1]
-    if return_margins:
-        return out, sum_lp, margins
-    return out, sum_lp
+    extra = ((margins,) if return_margins else ()) + ((no_speech,) if return_no_speech else ())
+    return (out, sum_lp) + extra
 
 
 # ----------------------------------------------------------------------------------------------
@@ -253,7 +259,8 @@ def beam_step_select(cand: list[tuple[float, int, int]], beam_size: int, eot: in
 
 
 def beam_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor, max_new_tokens: int,
-                beam_size: int = 5, patience: float = 1.0, return_all: bool = False):
+                beam_size: int = 5, patience: float = 1.0, return_all: bool = False, logit_noise: float = 0.0,
+                noise_seed: int = 0):
     """Beam search at temperature 0 as published in OpenAI Whisper's `BeamSearchDecoder.update/finalize` +
     `MaximumLikelihoodRanker(length_penalty=None)` -- the algorithm faster-whisper / CTranslate2 run for
     `beam_size=5, patience=1, length_penalty=1` (PARITY UNPINNED against CTranslate2, see the module header):
@@ -274,7 +281,11 @@ def beam_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor
     st = DecoderState(W, dims, enc_out.repeat_interleave(K, 0))
     sup = suppress_mask_for(spec)
     prompt = torch.tensor([list(spec.sot_sequence)] * (B * K), dtype=torch.long)
-    logits = st.step(prompt)[:, -1]
+    ng = torch.Generator().manual_seed(noise_seed)
+
+    def perturb(lg):   # stability probe (beam_stable_windows): uniform logit noise of the size of bf16 rounding
+        return lg + logit_noise * (2 * torch.rand(lg.shape, generator=ng) - 1) if logit_noise else lg
+    logits = perturb(st.step(prompt)[:, -1])
     gen = [[[] for _ in range(K)] for _ in range(B)]
     cum = [[0.0] + [float("-inf")] * (K - 1) for _ in range(B)]
     finished = [[] for _ in range(B)]     # (tokens, score, length)
@@ -308,7 +319,7 @@ def beam_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor
             break
         for i in range(dims.n_text_layer):
             st.self_kv[i] = (st.self_kv[i][0][src], st.self_kv[i][1][src])
-        logits = st.step(nxt_tok[:, None])[:, -1]
+        logits = perturb(st.step(nxt_tok[:, None])[:, -1])
     out = torch.full((B, max_new_tokens), eot, dtype=torch.long)
     sum_lp = torch.zeros(B)
     pools = []
@@ -327,3 +338,19 @@ def beam_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor
     if return_all:
         return out, sum_lp, pools, finished
     return out, sum_lp
+
+
+def beam_stable_windows(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tensor, max_new_tokens: int,
+                        ref_tokens: torch.Tensor, beam_size: int = 5, noise: float = 0.03, trials: int = 3) -> list[bool]:
+    """Which windows have a beam-search result that a bf16 implementation can be held to: a beam search takes
+    beam_size x (beam_size + 1) discrete decisions per step, so a near-tie at ANY step may legitimately resolve
+    differently under bf16 rounding and change which hypotheses reach the pool. A window is `stable` when the
+    unperturbed result `ref_tokens` is reproduced under `trials` independent uniform logit perturbations of +-`noise`
+    (the size of the bf16 logit error measured on the GPU)."""
+    stable = [True] * enc_out.shape[0]
+    for t in range(trials):
+        tok, _ = beam_decode(W, dims, spec, enc_out, max_new_tokens, beam_size=beam_size, logit_noise=noise,
+                             noise_seed=1000 + t)
+        for b in range(enc_out.shape[0]):
+            stable[b] = stable[b] and bool(torch.equal(tok[b], ref_tokens[b]))
+    return stable

@@ -8,7 +8,7 @@ from janus_b200.whisper.weights import init_random_weights
 B = int(os.environ.get("B", "1024"))
 dims = PRESETS["small"]
 eng = WhisperEngine(dims, init_random_weights(dims, seed=0, profile="confident"))
-ses = DecodeSession(eng, B, 128, steps_per_graph=8, fused=bool(int(os.environ.get("FUSED", "0"))))
+ses = DecodeSession(eng, B, 128, steps_per_graph=8)
 enc = torch.randn(B, 1500, dims.n_audio_state, device="cuda").bfloat16()
 ses._ensure_graph(); ses.cross_kv(enc); ses.reset()
 ses.run_steps(64)

@@ -140,13 +140,14 @@ def decode_cases(n_new=16, beam=5):
         with torch.no_grad():
             g_tok, g_lp, margins = R.greedy_decode(W, dims, spec, enc, n_new, return_margins=True)
             b_tok, b_lp, pools, finished = R.beam_decode(W, dims, spec, enc, n_new, beam_size=beam, return_all=True)
+            stable = R.beam_stable_windows(W, dims, spec, enc, n_new, b_tok, beam_size=beam)
         case = {"greedy_tokens": g_tok.tolist(), "greedy_sum_logprob": [round(float(v), 4) for v in g_lp],
                 "greedy_min_margin": [round(float(m[torch.isfinite(m)].min()), 4) for m in margins],
                 "beam_tokens": b_tok.tolist(), "beam_sum_logprob": [round(float(v), 4) for v in b_lp],
                 "beam_decisive": [], "finished": []}
         for b in range(enc.shape[0]):
             ranked = sorted((p[1] / max(p[2], 1) for p in pools[b]), reverse=True)
-            case["beam_decisive"].append(bool(len(ranked) < 2 or ranked[0] - ranked[1] > 0.05))
+            case["beam_decisive"].append(bool(stable[b] and (len(ranked) < 2 or ranked[0] - ranked[1] > 0.05)))
             case["finished"].append([{"tokens": f[0], "score": round(float(f[1]), 4), "len": f[2]} for f in finished[b]])
         out["cases"][name] = case
     return out

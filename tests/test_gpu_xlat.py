@@ -33,12 +33,25 @@ def test_xlat_matches_float32(n, T, d, H):
     assert err < 2e-2, err
 
 
-def test_xlat_streaming_variant_env():
+def test_xlat_streaming_variant_both_in_one_process():
     """d = 1024 (Whisper-medium) does not fit the one-tile ring and runs the streaming two-pass kernel; the same
-    kernel can be forced for small d with JANUS_XLAT_STREAM=1 (read once per process, so only documented here)."""
+    kernel is selected for small d with janus_set_option(JANUS_OPT_XLAT_STREAM, 1) -- an explicit call, so both variants
+    are exercised here in one process and must agree with float32 (and closely with each other)."""
+    from janus_b200 import _abi
     z, ref = _run(3, 1500, 1024, 16, seed=5)
     scale = ref.abs().amax(dim=-1, keepdim=True).clamp_min(1e-3)
     assert ((z - ref).abs() / scale).max().item() < 2e-2
+    za, ref = _run(5, 1500, 768, 12, seed=9)
+    try:
+        _abi.set_option(_abi.OPT_XLAT_STREAM, 1)
+        zb, _ = _run(5, 1500, 768, 12, seed=9)
+    finally:
+        _abi.set_option(_abi.OPT_XLAT_STREAM, -1)
+    scale = ref.abs().amax(dim=-1, keepdim=True).clamp_min(1e-3)
+    assert ((za - ref).abs() / scale).max().item() < 2e-2 and ((zb - ref).abs() / scale).max().item() < 2e-2
+    assert ((za - zb).abs() / scale).max().item() < 2e-2
+    zc, _ = _run(5, 1500, 768, 12, seed=9)
+    assert torch.equal(za, zc)          # back on the default kernel: bit-identical to the first run
 
 
 def test_xlat_sharp_distribution_rescales():

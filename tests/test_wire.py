@@ -70,3 +70,47 @@ def test_rich_prosody_fields_reach_the_receiver_as_numbers():
     back = JanusPacket.deserialize(pkt)
     assert isinstance(back.prosody['avg_pitch_hz'], float) and back.prosody['avg_pitch_hz'] == 312.5
     assert back.prosody['avg_energy'] == 0.21 and wire.emotion_tag(back) == 'Excited'
+
+
+def test_voice_verify_similarity_rule():
+    """endpoints.py:58-63 on host strings (the GPU leg is tests/test_gpu_transcribe.py)."""
+    from janus_b200.services.verify import SIMILARITY_THRESHOLD, verify_file, verify_transcript
+    phrase = "The quick brown fox jumps over the lazy dog"
+    assert SIMILARITY_THRESHOLD == 0.8
+    assert verify_transcript("  the quick brown fox jumps over the lazy dog ", phrase) == (True, 1.0)
+    ok, r = verify_transcript("the quick brown fox jumped over a lazy dog", phrase)
+    assert ok and 0.8 <= r < 1.0
+    ok, r = verify_transcript("hello there", phrase)
+    assert not ok and r < 0.8
+
+    class T:
+        def __init__(self, out): self.out = out
+        def transcribe_file(self, p):
+            if isinstance(self.out, Exception):
+                raise self.out
+            return self.out
+    assert verify_file(T(phrase.upper()), "x.wav", phrase) == {"status": "verified"}
+    assert verify_file(T("nope"), "x.wav", phrase) == {"status": "failed", "transcript": "nope"}
+    assert verify_file(T(ValueError("bad wav")), "x.wav", phrase) == {"status": "failed", "transcript": "bad wav"}
+
+
+def test_split_window_segments_rules():
+    """The segment / seek rule of the utterance loop (services/transcriber.py; faster-whisper generate_segments)."""
+    from janus_b200.services.transcriber import split_window_segments
+    tb = 1000
+    # <0.00> a b <1.00><1.00> c <2.00>  -> two segments, ends in a single timestamp: whole window consumed
+    segs, adv = split_window_segments([tb, 1, 2, tb + 50, tb + 50, 3, tb + 100], tb, 3000)
+    assert [s[:2] for s in segs] == [(0, 50), (50, 100)] and adv == 3000
+    assert segs[0][2] == [tb, 1, 2, tb + 50] and segs[1][2] == [tb + 50, 3, tb + 100]
+    # ends with a consecutive pair -> seek advances to that timestamp (2 frames per 0.02 s position)
+    segs, adv = split_window_segments([tb, 1, tb + 40, tb + 40, 2, tb + 90, tb + 90], tb, 3000)
+    assert [s[:2] for s in segs] == [(0, 40), (40, 90)] and adv == 180
+    # tokens after the last pair are dropped from this window and re-decoded from the new seek
+    segs, adv = split_window_segments([tb, 1, tb + 40, tb + 40, 2, 3], tb, 3000)
+    assert [s[:2] for s in segs] == [(0, 40)] and adv == 80
+    # no consecutive pair: one segment, duration from the last timestamp, whole window consumed
+    segs, adv = split_window_segments([tb + 5, 1, 2, 3], tb, 1200)
+    assert segs == [(0, 5, [tb + 5, 1, 2, 3])] and adv == 1200
+    segs, adv = split_window_segments([1, 2], tb, 1200)
+    assert segs == [(0, 600, [1, 2])] and adv == 1200
+    assert split_window_segments([], tb, 700) == ([(0, 350, [])], 700)
