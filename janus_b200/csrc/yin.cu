@@ -336,6 +336,29 @@ __global__ void prosody_reduce_kernel(const float* __restrict__ f0, const float*
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Per-chunk speech gate for many sessions: the step BEFORE the path.
+// The reference asks Silero VAD per 1536-sample chunk (services/vad.py:40-77, engine.py:471-493); its model is a
+// download and not on the path. This gate reuses what K4 already computes for the chunk's hops: a chunk is speech
+// when its loudest hop exceeds level_db AND at least min_voiced of its hops are voiced (YIN found a period and
+// the hop passed aubio's -50 dB silence gate). One thread per chunk; chunks are hops_per_chunk consecutive hops.
+// ------------------------------------------------------------------------------------------
+__global__ void vad_gate_kernel(const float* __restrict__ f0, const float* __restrict__ hop_db, long long n_chunks,
+                                int hops_per_chunk, float level_db, int min_voiced, uint8_t* __restrict__ flags,
+                                float* __restrict__ chunk_db) {
+  const long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_chunks) return;
+  float mx = -INFINITY;
+  int voiced = 0;
+  for (int h = 0; h < hops_per_chunk; ++h) {
+    const long long i = c * hops_per_chunk + h;
+    mx = fmaxf(mx, hop_db[i]);
+    voiced += f0[i] > 0.f;
+  }
+  flags[c] = (mx > level_db && voiced >= min_voiced) ? 1 : 0;
+  if (chunk_db) chunk_db[c] = mx;
+}
+
 }  // namespace janus
 
 using namespace janus;
@@ -402,5 +425,17 @@ extern "C" int32_t janus_prosody_reduce_f32(const float* f0, const float* hop_su
       f0, hop_sumsq, hop_offsets, stream_lengths, n_streams, scratch, rms_out, mean_f0_out,
       n_voiced_out, tags_out);
   JANUS_LAUNCH_CHECK("prosody_reduce_kernel");
+  return JANUS_OK;
+}
+
+extern "C" int32_t janus_vad_gate_f32(const float* f0, const float* hop_db, int64_t n_chunks, int32_t hops_per_chunk,
+                                      float level_db, int32_t min_voiced, uint8_t* flags_out, float* chunk_db_out,
+                                      void* stream) {
+  if (n_chunks <= 0) return JANUS_OK;
+  JANUS_CHECK_ARG(f0 && hop_db && flags_out, "vad_gate: null pointer");
+  JANUS_CHECK_ARG(hops_per_chunk >= 1 && min_voiced >= 0 && min_voiced <= hops_per_chunk, "vad_gate: bad hop counts");
+  vad_gate_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      f0, hop_db, n_chunks, hops_per_chunk, level_db, min_voiced, flags_out, chunk_db_out);
+  JANUS_LAUNCH_CHECK("vad_gate_kernel");
   return JANUS_OK;
 }

@@ -13,6 +13,7 @@ from dataclasses import dataclass
 import numpy as np
 import torch
 
+from ._device import on_device
 from .protocol import JanusMode, pack_packets
 from .services.prosody import ENERGY_TAGS, PITCH_TAGS, ProsodyEngine
 from .whisper.config import PRESETS, WhisperDims, detokenize, tokenizer_spec
@@ -190,6 +191,7 @@ class SemanticEncoder:
         return enc + self.lanes_per_call * ses.n_steps * ses.kernels_per_step
 
     # ---- the path -------------------------------------------------------------------------
+    @on_device
     def encode_lane_front(self, lane: _Lane, pcm: torch.Tensor, lengths: tuple) -> None:
         """Prosody + K1 + K2 + cross-K/V of one lane's windows; call under the encoder stream."""
         plan, offs, lens = self._lane_plan(lengths)
@@ -201,6 +203,7 @@ class SemanticEncoder:
         enc = self.encode_lane_windows(pcm, offs, lens, out=lane.session.enc_target())
         lane.session.cross_kv(enc)
 
+    @on_device
     def encode_lane_windows(self, pcm: torch.Tensor, offs: torch.Tensor, lens: torch.Tensor,
                             out: torch.Tensor | None = None) -> torch.Tensor:
         """K1 + K2 over one lane's windows in encoder micro-batches; fills `out` (a latent decode session's own
@@ -213,6 +216,7 @@ class SemanticEncoder:
             self.whisper.encode(self.mel_pad[:n], out=enc_out[c0:c0 + n])
         return enc_out
 
+    @on_device
     def encode_device(self, pcm: torch.Tensor, lengths, host_pcm: torch.Tensor | None = None) -> EncodeResult:
         """pcm: float32 device tensor holding the `batch` windows concatenated (source-rate samples);
         lengths: per-window sample counts. If `host_pcm` (pinned) is given, each lane's slice is first
@@ -264,6 +268,7 @@ class SemanticEncoder:
             start += n
         return EncodeResult(tokens, sum_lp, tags, events, mean_f0, rms)
 
+    @on_device
     def synchronize(self) -> None:
         self.enc_stream.synchronize()
         for lane in self.lanes:

@@ -103,6 +103,12 @@ class MultiSessionSegmenter:
         if utt is not None:
             self.ready.append((session_id, utt))
 
+    def push_tick(self, session_ids, chunks: np.ndarray, speech) -> None:
+        """One chunk of EVERY session at once: chunks [n, CHUNK_SIZE], speech [n] bool (e.g. the flags of
+        janus_b200.vad.GpuVadGate.step for this tick)."""
+        for sid, chunk, sp in zip(session_ids, chunks, speech):
+            self.push(sid, chunk, bool(sp))
+
     def take(self, max_items: int | None = None) -> list[tuple[object, np.ndarray]]:
         """Removes and returns up to `max_items` finished (session_id, utterance) pairs, oldest first."""
         n = len(self.ready) if max_items is None else min(max_items, len(self.ready))

@@ -7,6 +7,7 @@ import ctypes as C
 import torch
 
 from .. import _abi
+from .._device import on_device
 from .config import TokenizerSpec, WhisperDims, tokenizer_spec
 from .frontend import LogMelFrontend
 
@@ -37,9 +38,12 @@ class WhisperEngine:
         self.dims = dims
         self.spec = spec or tokenizer_spec(dims)
         self._keep: list[torch.Tensor] = []   # owns every device tensor referenced by the C structs
-        self.frontend = LogMelFrontend(dims.n_mels, self.device)
-        self._pack_encoder(weights)
-        self._pack_decoder(weights)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        with torch.cuda.device(self.device):
+            self.frontend = LogMelFrontend(dims.n_mels, self.device)
+            self._pack_encoder(weights)
+            self._pack_decoder(weights)
         self._enc_ws: torch.Tensor | None = None
 
     # ---- packing ----------------------------------------------------------------------------
@@ -82,6 +86,7 @@ class WhisperEngine:
         self.enc_weights = ew
 
     # ---- encoder ------------------------------------------------------------------------------
+    @on_device
     def encode(self, mel_pad: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
         """mel_pad: bf16 [B, 2*n_ctx+2, n_mels] (LogMelFrontend output) -> bf16 [B, n_ctx, d]."""
         d = self.dims
@@ -325,6 +330,7 @@ class DecodeSession:
         if beam:
             self.kernels_per_step += 1   # candidates + update instead of pick
 
+    @on_device
     def _step(self) -> None:
         e = self.eng
         if self.beam_state is not None:
@@ -334,6 +340,7 @@ class DecodeSession:
         _abi.call("janus_whisper_decode_step", C.byref(e.c_dec_dims), C.byref(e.dec_weights), C.byref(self.state),
                   torch.cuda.current_stream(e.device).cuda_stream)
 
+    @on_device
     def set_prompt(self, prompt) -> None:
         """Replaces the forced prefix by another one of the SAME length (the length is baked into the captured
         step; the tokens are data)."""
@@ -344,6 +351,7 @@ class DecodeSession:
         self.prompt.copy_(torch.tensor(prompt, dtype=torch.int32))
         self.sot_index = max(i for i, t in enumerate(prompt) if t == spec.sot) if spec.sot in prompt else 0
 
+    @on_device
     def no_speech_prob(self) -> torch.Tensor:
         """softmax(logits)[<|nospeech|>] per row, fp32 device tensor. Only meaningful right after the step that
         consumed <|startoftranscript|> (step index `sot_index`): that is the distribution faster-whisper /
@@ -351,6 +359,7 @@ class DecodeSession:
         V = self.eng.dims.n_vocab
         return torch.softmax(self.logits[:, :V], dim=-1)[:, self.eng.spec.no_speech].clone()
 
+    @on_device
     def finalize(self):
         """Beam search: ranks every window's finished / live hypotheses (score / n_tokens) into best_tokens /
         best_score / best_len. Enqueued on the current stream."""
@@ -360,6 +369,7 @@ class DecodeSession:
                   torch.cuda.current_stream(e.device).cuda_stream)
         return self.best_tokens[:, self.n_prompt:], self.best_score
 
+    @on_device
     def reset(self, forced: torch.Tensor | None = None) -> None:
         self.tokens.zero_()
         self.tokens[:, :self.n_prompt] = self.prompt
@@ -385,6 +395,7 @@ class DecodeSession:
         this session's windows into (None for K/V sessions, which copy what they need in cross_kv)."""
         return self.enc_buf if self.latent else None
 
+    @on_device
     def cross_kv(self, enc_out: torch.Tensor) -> None:
         e = self.eng
         assert enc_out.shape[0] == self.n_windows and enc_out.dtype == torch.bfloat16 and enc_out.is_contiguous()
@@ -396,6 +407,7 @@ class DecodeSession:
                   C.byref(e.c_dec_dims), C.byref(e.dec_weights), enc_out.data_ptr(), self.n_windows, self.cross_k.data_ptr(), self.cross_v.data_ptr(),
                   torch.cuda.current_stream(e.device).cuda_stream)
 
+    @on_device
     def _ensure_graph(self) -> None:
         if not self.use_graph or self.graph is not None:
             return
@@ -417,6 +429,7 @@ class DecodeSession:
                     self._step()
             self.tail_graph = t
 
+    @on_device
     def run_steps(self, n_steps: int | None = None) -> None:
         """Enqueues n_steps decode steps (default: all) on the current stream."""
         n = self.n_steps if n_steps is None else n_steps
@@ -434,6 +447,7 @@ class DecodeSession:
                 for _ in range(rem):
                     self._step()
 
+    @on_device
     def decode(self, enc_out: torch.Tensor, forced: torch.Tensor | None = None, n_steps: int | None = None):
         """Returns (tokens [n_windows, max_new] int32 device, sum_logprob [n_windows]); with beam search those of the
         best hypothesis of every window. Does not synchronise."""

@@ -10,6 +10,7 @@ import numpy as np
 import torch
 
 from .. import _abi
+from .._device import on_device
 
 N_FFT, HOP, SR, N_BINS, N_FRAMES = 400, 160, 16000, 201, 3000
 
@@ -55,6 +56,7 @@ class LogMelFrontend:
         self.mel_w = torch.from_numpy(packed).to(device)
         self.frames_alloc = int(_abi.lib().janus_logmel_frames_alloc())
 
+    @on_device
     def __call__(self, pcm: torch.Tensor, offsets: torch.Tensor, lengths: torch.Tensor, decim: int = 1,
                  want_bf16: bool = True, want_f32: bool = False, scratch=None, out_bf16=None):
         """pcm float32 device (streams concatenated), offsets/lengths int64 device [n] (source-rate
@@ -80,6 +82,7 @@ class LogMelFrontend:
         (+160 zero samples, centred STFT at hop 160, last frame dropped); content_frames = n_frames - 1."""
         return (-(-n_samples // decim) + 160) // HOP
 
+    @on_device
     def utterance(self, pcm: torch.Tensor, offsets: torch.Tensor, lengths: torch.Tensor, nf_alloc: int, decim: int = 1):
         """Pass 1 over whole utterances: (scratch fp32 [n, nf_alloc, n_mels] log10-mel, maxbuf int32 [n])."""
         n, dev = int(offsets.numel()), self.device
@@ -90,6 +93,7 @@ class LogMelFrontend:
                   scratch.data_ptr(), nf_alloc, maxbuf.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
         return scratch, maxbuf
 
+    @on_device
     def windows(self, scratch: torch.Tensor, maxbuf: torch.Tensor, lengths: torch.Tensor, win_utt, win_seek,
                 decim: int = 1, want_f32: bool = False):
         """Pass 2: window w = frames [win_seek[w], +3000) of utterance win_utt[w], clamped with that utterance's

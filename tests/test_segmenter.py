@@ -94,3 +94,19 @@ def test_multi_session_interleaved_equals_per_session():
         assert len(mine) == len(ref)
         for a, b in zip(mine, ref):
             assert np.array_equal(a, b)
+
+
+def test_push_tick_equals_per_session_push():
+    from janus_b200.segmenter import MultiSessionSegmenter
+    rng = np.random.default_rng(5)
+    a, b = MultiSessionSegmenter(), MultiSessionSegmenter()
+    for t in range(80):
+        chunks = rng.standard_normal((4, 1536)).astype(np.float32)
+        speech = rng.random(4) < (0.7 if (t // 20) % 2 == 0 else 0.02)
+        a.push_tick(range(4), chunks, speech)
+        for s in range(4):
+            b.push(s, chunks[s], bool(speech[s]))
+    ra, rb = a.take(), b.take()
+    assert len(ra) == len(rb) > 0
+    for (sa, ua), (sb, ub) in zip(ra, rb):
+        assert sa == sb and np.array_equal(ua, ub)
