@@ -33,7 +33,8 @@ def run_utterance_mode(args) -> None:
     """Real-arrival streaming run. Every session delivers one 1536-sample chunk (48 kHz) per 32 ms of WALL time
     (the reference's cadence, audio_io.py:28-29). Per tick: H2D of all sessions' chunks -> GpuVadGate (stateful YIN per
     session + vad_gate_kernel) -> flags -> MultiSessionSegmenter (engine.py:471-506). Finished utterances are encoded in
-    service calls of up to --service-batch windows: stateful prosody (the session's sliding buffer carried between its
+    service calls of up to --service-batch windows (started when the batch is full or the oldest utterance has waited
+    --max-wait-ms): stateful prosody (the session's sliding buffer carried between its
     utterances) + STT on the utterance padded in feature space -> packets. Latency of an utterance = packet bytes
     ready - wall time at which its last chunk had arrived. Single host thread: while a service call runs, ticks queue
     up and are processed late (their lateness is reported and is part of the latency)."""
@@ -127,7 +128,13 @@ def run_utterance_mode(args) -> None:
         for sid, utt in seg.take():
             pending.append((sid, utt))
             pending_arr.append(due)
-        if pending:
+        # batching policy: a service call costs a whole --service-batch of windows whatever it carries, so wait
+        # until it is full or the oldest finished utterance has waited --max-wait-ms
+        # (the wait rule only applies while the tick loop is on time: when it is behind, overdue ticks are drained first --
+        # they take ~3 ms each -- so that the backlog is served in FULL batches instead of one small batch per tick)
+        on_time = lateness[-1] < tick_s
+        if pending and (len(pending) >= Bq or t == n_ticks - 1 or
+                        (on_time and now() - pending_arr[0] >= args.max_wait_ms / 1e3)):
             items, arr = pending[:Bq], pending_arr[:Bq]
             pending, pending_arr = pending[Bq:], pending_arr[Bq:]
             ts = now()
@@ -151,7 +158,7 @@ def run_utterance_mode(args) -> None:
                         "(stateful YIN per session + vad_gate_kernel) -> utterance state machine -> stateful prosody + STT "
                         "(utterance padded in feature space) -> packets", "model": args.model, "sessions": args.sessions,
             "n_gpus": world, "sessions_per_gpu": S, "new_tokens_per_utterance": args.new_tokens,
-            "service_batch": Bq, "wall_seconds": wall_s, "ticks": n_ticks,
+            "service_batch": Bq, "max_wait_ms": args.max_wait_ms, "wall_seconds": wall_s, "ticks": n_ticks,
             "utterances_encoded": int(counts[0]), "service_calls": int(counts[1]), "left_pending": int(counts[2]),
             "latency_ms": {"p50": p50, "p99": p99, "max": pmax}, "tick_lateness_ms_p99": late99,
             "service_utilisation": util, "keeps_up": late99 < 1000.0 and int(counts[2]) <= Bq * world,
@@ -173,7 +180,10 @@ def main() -> None:
                     help="chunks: every 1 s chunk of every session is encoded (virtual-clock replay of measured service "
                          "times); utterance: REAL-ARRIVAL run -- 48 kHz sessions tick every 32 ms of wall time, the GPU "
                          "speech gate + the reference's utterance state machine decide what is encoded")
-    ap.add_argument("--service-batch", type=int, default=128, help="utterance mode: windows per service call")
+    ap.add_argument("--service-batch", type=int, default=64, help="utterance mode: windows per service call")
+    ap.add_argument("--max-wait-ms", type=float, default=100.0,
+                    help="utterance mode: a service call starts when --service-batch utterances are pending or the "
+                         "oldest has waited this long")
     args = ap.parse_args()
     if args.mode == "utterance":
         return run_utterance_mode(args)

@@ -219,7 +219,8 @@ def run_gpu_stt(args) -> None:
     enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
                           prosody_sample_rate=sr, input_sample_rate=sr, lane_batch=args.lane_batch,
                           n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph,
-                          enc_chunk=getattr(args, "enc_chunk", 64), beam=getattr(args, "beam", 0))
+                          enc_chunk=getattr(args, "enc_chunk", 64), beam=getattr(args, "beam", 0),
+                          pace_encoder=getattr(args, "pace_encoder", False))
     beam = max(getattr(args, "beam", 0), 1)
     N = int(round(seconds * sr))
     x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)

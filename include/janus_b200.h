@@ -97,9 +97,9 @@ int32_t janus_prosody_reduce_f32(const float* f0, const float* hop_sumsq, const 
 
 /* Per-chunk speech gate for many sessions, from the outputs of janus_yin_frames_f32 (the step before the path:
  * backend/services/engine.py:471-493 asks backend/services/vad.py per 1536-sample chunk; Silero's model is a download,
- * so this is an energy + periodicity gate, NOT a reproduction of Silero's decisions). Chunk c = hops
+ * so this is an energy gate (two thresholds), NOT a reproduction of Silero's decisions). Chunk c = hops
  * [c*hops_per_chunk, (c+1)*hops_per_chunk) of f0 / hop_db; flags_out[c] = 1 iff max hop level > level_db and at
- * least min_voiced hops have f0 > 0. chunk_db_out (or NULL) receives the max hop level. */
+ * least min_voiced hops have f0 > 0 (passed aubio's -50 dB silence gate). chunk_db_out (or NULL) receives the max hop level. */
 int32_t janus_vad_gate_f32(const float* f0, const float* hop_db, int64_t n_chunks, int32_t hops_per_chunk,
                            float level_db, int32_t min_voiced, uint8_t* flags_out, float* chunk_db_out, void* stream);
 

@@ -29,6 +29,8 @@ constexpr int LM_BINS = 201;
 constexpr int LM_FRAMES = 3000;      // encoder window
 constexpr int LM_TAIL_PAD = 160;     // FeatureExtractor(padding=160)
 constexpr int LM_WARPS = 8;
+constexpr int LM_ZLD = 21;         // row stride of Z in float2: 20 would put lanes k1 and k1 + 4 of stage 2 on the same banks
+constexpr int LM_WARP_FLOATS = 400 + 2 * 20 * LM_ZLD + 208;   // per warp: xs[400] | Z[20][LM_ZLD] float2 | P[208]
 
 __constant__ float2 c_w20[20];
 __constant__ float2 c_w400[400];
@@ -77,7 +79,7 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
   float* s_melw = s_hann + 400;                                  // n_mels * mel_max_len
   int* s_mstart = reinterpret_cast<int*>(s_melw + n_mels * mel_max_len);
   int* s_mlen = s_mstart + n_mels;
-  float* s_warp = reinterpret_cast<float*>(s_mlen + n_mels);     // per warp: xs[400] | Z[400] float2 | P[208]
+  float* s_warp = reinterpret_cast<float*>(s_mlen + n_mels);     // per warp: LM_WARP_FLOATS
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < 20; i += blockDim.x) s_w20[i] = c_w20[i];
   for (int i = threadIdx.x; i < 400; i += blockDim.x) { s_w400[i] = c_w400[i]; s_hann[i] = c_hann[i]; }
@@ -93,9 +95,9 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
   const int t = blockIdx.x * LM_WARPS + warp;
   if (t >= nf) return;
 
-  float* xs = s_warp + warp * (400 + 800 + 208);
+  float* xs = s_warp + warp * LM_WARP_FLOATS;
   float2* Z = reinterpret_cast<float2*>(xs + 400);
-  float* P = xs + 1200;
+  float* P = xs + 400 + 2 * 20 * LM_ZLD;
   const float* src = pcm + offsets[b];
   for (int n = lane; n < LM_NFFT; n += 32) {
     int64_t i = (int64_t)t * LM_HOP - LM_NFFT / 2 + n;
@@ -119,8 +121,8 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
       tw += k1;
       if (tw >= 20) tw -= 20;
     }
-    Z[k1 * 20 + n2] = cmul(make_float2(re, im), s_w400[n2 * k1]);
-    if (k1 >= 1 && k1 <= 9) Z[(20 - k1) * 20 + n2] = cmul(make_float2(re, -im), s_w400[n2 * (20 - k1)]);
+    Z[k1 * LM_ZLD + n2] = cmul(make_float2(re, im), s_w400[n2 * k1]);
+    if (k1 >= 1 && k1 <= 9) Z[(20 - k1) * LM_ZLD + n2] = cmul(make_float2(re, -im), s_w400[n2 * (20 - k1)]);
   }
   __syncwarp();
   // stage 2: the 201 bins, power spectrum
@@ -128,7 +130,7 @@ logmel_frames_kernel(const float* __restrict__ pcm, const int64_t* __restrict__ 
     const int k2 = k / 20, k1 = k - k2 * 20;
     float re = 0.f, im = 0.f;
     int tw = 0;
-    const float2* z = Z + k1 * 20;
+    const float2* z = Z + k1 * LM_ZLD;
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) {
       const float2 a = z[n2];
@@ -201,7 +203,7 @@ static int32_t logmel_frames(const float* pcm, const int64_t* offsets, const int
   if (rc) return rc;
   JANUS_CUDA(cudaMemsetAsync(maxbuf, 0x80, sizeof(int32_t) * n, st));
   const size_t smem = sizeof(float2) * 420 + sizeof(float) * 400 + sizeof(float) * n_mels * mel_max_len +
-                      sizeof(int) * 2 * n_mels + sizeof(float) * LM_WARPS * (400 + 800 + 208);
+                      sizeof(int) * 2 * n_mels + sizeof(float) * LM_WARPS * LM_WARP_FLOATS;
   JANUS_CUDA(cudaFuncSetAttribute(logmel_frames_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const dim3 grid((nf_alloc + LM_WARPS - 1) / LM_WARPS, n);
   logmel_frames_kernel<<<grid, LM_WARPS * 32, smem, st>>>(pcm, offsets, lengths, decim, n_mels, mel_start, mel_len,

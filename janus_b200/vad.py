@@ -2,7 +2,7 @@
 
 The reference gates one microphone per 1536-sample chunk (32 ms at 48 kHz) with Silero VAD on the CPU
 (/root/reference/backend/services/vad.py:40-77, called from engine.py:471-475). Silero's model is a download, so the
-gate here is an energy + periodicity decision built from what the prosody kernel already computes per hop: every
+gate here is an energy decision built from what the prosody kernel already computes per hop: every
 session keeps its own YIN sliding buffer on the device (as the reference's aubio object does), one launch of
 `yin_frames_kernel` serves the current chunk of ALL sessions, and `vad_gate_kernel` turns the three hops of a chunk
 into one flag. `MultiSessionSegmenter.push_tick` then runs the reference's utterance state machine per session.

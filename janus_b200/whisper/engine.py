@@ -430,8 +430,9 @@ class DecodeSession:
             self.tail_graph = t
 
     @on_device
-    def run_steps(self, n_steps: int | None = None) -> None:
-        """Enqueues n_steps decode steps (default: all) on the current stream."""
+    def run_steps(self, n_steps: int | None = None, after_replay=None) -> None:
+        """Enqueues n_steps decode steps (default: all) on the current stream. `after_replay()` (optional) is called
+        after every graph replay has been enqueued (the engine records pacing events there)."""
         n = self.n_steps if n_steps is None else n_steps
         if self.graph is None:
             for _ in range(n):
@@ -440,6 +441,8 @@ class DecodeSession:
         full, rem = divmod(n, self.steps_per_graph)
         for _ in range(full):
             self.graph.replay()
+            if after_replay is not None:
+                after_replay()
         if rem:
             if rem == self.n_steps % self.steps_per_graph and self.tail_graph is not None:
                 self.tail_graph.replay()

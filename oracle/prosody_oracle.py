@@ -174,7 +174,7 @@ class ProsodyOracle:
 def vad_gate_ref(f0: np.ndarray, hop_db: np.ndarray, hops_per_chunk: int, level_db: float = -40.0,
                  min_voiced: int = 1) -> np.ndarray:
     """CPU restatement of janus_vad_gate_f32 (janus_b200/csrc/yin.cu): chunk = hops_per_chunk consecutive hops; speech
-    iff its loudest hop exceeds level_db and at least min_voiced hops are voiced. (An energy + periodicity gate in the
+    iff its loudest hop exceeds level_db and at least min_voiced hops are voiced. (An energy gate with two thresholds in the
     place where the reference asks Silero VAD, backend/services/vad.py:40-77 -- not a restatement of Silero.)"""
     f0 = np.asarray(f0, np.float32).reshape(-1, hops_per_chunk)
     db = np.asarray(hop_db, np.float32).reshape(-1, hops_per_chunk)

@@ -181,3 +181,43 @@ def test_small_engine_lane128_latent_grouped_gemm_vs_oracle():
     # determinism of the route: a second call reproduces the first bit for bit
     res2 = enc.encode_device(pcm, lengths).synchronize()
     assert torch.equal(res2.tokens.cpu(), tok)
+
+
+def test_large_v3_full_depth_encoder_greedy_and_beam5_spot_check():
+    """BASELINE configs[3] at FULL depth: Whisper-large-v3 (128 mels, d = 1280, 20 heads, 32 + 32 layers, 1.55 B
+    random-init parameters), one 12 s window from audio: encoder states against the fp32 oracle, greedy tokens per the
+    free-running statement, and the beam-5 best hypothesis where the oracle's result is stable under +-0.03 logit noise.
+    Short (6 new tokens): the fp32 CPU oracle reads 6 GB of weights per decode step."""
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import PRESETS, tokenizer_spec
+    from janus_b200.whisper.engine import DecodeSession, WhisperEngine
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = PRESETS["large-v3"]
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=0, profile="confident")
+    clip = make_clips(1, 12.0, 16000, seed=1234).numpy()[0]
+    n_new = 6
+    with torch.no_grad():
+        mel = torch.from_numpy(log_mel_window(clip, dims.n_mels))[None]
+        enc_ref = R.encode(W, dims, mel)
+        g_tok, g_lp, margins = R.greedy_decode(W, dims, spec, enc_ref, n_new, return_margins=True)
+        b_tok, b_lp = R.beam_decode(W, dims, spec, enc_ref, n_new, beam_size=5)
+        stable = R.beam_stable_windows(W, dims, spec, enc_ref, n_new, b_tok, beam_size=5, trials=2)
+    eng = WhisperEngine(dims, W, torch.device("cuda", 0))
+    enc = _gpu_encode(eng, [clip])
+    err = (enc.float().cpu() - enc_ref).abs()
+    print(f"large-v3 encoder (32 layers) vs fp32 oracle: mean |err| {err.mean():.4g} max {err.max():.4g}")
+    assert err.mean() <= 2e-2 and err.max() <= 0.5
+    ses = DecodeSession(eng, batch=1, max_new_tokens=n_new)
+    toks, _ = ses.decode(enc)
+    torch.cuda.synchronize()
+    check_free_running(toks, g_tok, margins, 0.25, "large-v3 greedy")
+    bs = DecodeSession(eng, batch=1, max_new_tokens=n_new, beam=5)
+    bt, blp = bs.decode(enc)
+    torch.cuda.synchronize()
+    print(f"large-v3 beam-5: oracle result stable under logit noise: {stable[0]}; tokens {bt[0].tolist()} vs {b_tok[0].tolist()}")
+    if stable[0]:
+        assert bt[0].cpu().long().tolist() == b_tok[0].tolist()
+        assert abs(float(blp[0]) - float(b_lp[0])) <= 0.3

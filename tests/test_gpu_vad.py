@@ -61,18 +61,21 @@ def test_gate_flags_and_utterances_match_the_oracle():
 
 
 def test_gate_min_voiced_and_level_are_inputs():
+    """level_db and min_voiced are inputs. `voiced` means f0 > 0, i.e. the hop passed aubio's -50 dB silence gate and
+    YIN returned a period -- with aubio's fallback to the global minimum that is true for any non-silent hop, noise
+    included, so min_voiced adds the -50 dB floor, not a periodicity test."""
     from janus_b200.synth import sine_wave
     from janus_b200.vad import GpuVadGate
     rng = np.random.default_rng(3)
     tone = sine_wave(200.0, 0.5, 48000, 0.3)[:1536 * 8].reshape(8, 1536)
-    noise = (0.05 * rng.standard_normal((8, 1536))).astype(np.float32)       # loud but aperiodic
-    g1 = GpuVadGate(2, min_voiced=1)
-    g0 = GpuVadGate(2, min_voiced=0)
+    faint = (1e-3 * rng.standard_normal((8, 1536))).astype(np.float32)       # about -60 dB: below aubio's gate
+    g1 = GpuVadGate(2, level_db=-100.0, min_voiced=1)
+    g0 = GpuVadGate(2, level_db=-100.0, min_voiced=0)
     quiet = GpuVadGate(2, level_db=-5.0, min_voiced=0)
-    f1 = np.array([g1.step(np.stack([tone[i], noise[i]])) for i in range(8)])
-    f0 = np.array([g0.step(np.stack([tone[i], noise[i]])) for i in range(8)])
-    fq = np.array([quiet.step(np.stack([tone[i], noise[i]])) for i in range(8)])
-    assert f1[3:, 0].all()                 # the tone is speech once the sliding buffer has filled
-    assert f0[:, 1].all()                  # pure energy gate: loud noise passes ...
-    assert not f1[:, 1].all()              # ... the periodicity requirement rejects (most of) it
-    assert not fq.any()                    # nothing is louder than -5 dB
+    f1 = np.array([g1.step(np.stack([tone[i], faint[i]])) for i in range(8)])
+    f0 = np.array([g0.step(np.stack([tone[i], faint[i]])) for i in range(8)])
+    fq = np.array([quiet.step(np.stack([tone[i], faint[i]])) for i in range(8)])
+    assert f1[:, 0].all() and f0[:, 0].all()   # the tone is speech under both settings
+    assert f0[:, 1].all()                       # level -100 dB alone lets the faint noise through ...
+    assert not f1[:, 1].any()                   # ... requiring a voiced hop applies aubio's -50 dB silence gate
+    assert not fq.any()                         # nothing is louder than -5 dB
