@@ -336,8 +336,6 @@ def main() -> None:
     ap.add_argument("--lanes", type=int, default=0, help="decode lanes in flight (0 = 2 x batch / lane_batch)")
     ap.add_argument("--steps-per-graph", type=int, default=10)
     ap.add_argument("--enc-chunk", type=int, default=64, help="encoder micro-batch (windows per encoder pass)")
-    ap.add_argument("--pace-encoder", action="store_true",
-                    help="spread the encoder micro-batches of call k+1 over the decode of call k (power-cap experiment)")
     ap.add_argument("--max-new-tokens", type=int, default=128)
     ap.add_argument("--beam", type=int, default=0,
                     help="0 = greedy (the reference's call: beam_size=1); K >= 1 = beam search with K beams per window "

@@ -55,7 +55,9 @@ def run_utterance_mode(args) -> None:
     S = len(shard_streams(args.sessions, world, rank))
     sr, tick_s = 48000, CHUNK_SIZE / 48000.0
     n_ticks = int(args.seconds / tick_s)
-    Bq = args.service_batch
+    Bq = args.service_batch if args.service_batch > 0 else max(16, S // 16)
+    if args.max_wait_ms <= 0:       # scale the batching wait with the per-GPU arrival rate as well
+        args.max_wait_ms = max(20.0, 100.0 * S / 1024.0)
     enc = SemanticEncoder(args.model, batch=Bq, max_new_tokens=args.new_tokens, device=dev, lane_batch=Bq, n_lanes=1,
                           prosody_sample_rate=sr, input_sample_rate=sr, steps_per_graph=args.new_tokens + 2)
     ses = enc.lanes[0].session
@@ -180,7 +182,8 @@ def main() -> None:
                     help="chunks: every 1 s chunk of every session is encoded (virtual-clock replay of measured service "
                          "times); utterance: REAL-ARRIVAL run -- 48 kHz sessions tick every 32 ms of wall time, the GPU "
                          "speech gate + the reference's utterance state machine decide what is encoded")
-    ap.add_argument("--service-batch", type=int, default=64, help="utterance mode: windows per service call")
+    ap.add_argument("--service-batch", type=int, default=64,
+                    help="utterance mode: windows per service call (0 = scale with the sessions per GPU: 64 per 1024, >= 16)")
     ap.add_argument("--max-wait-ms", type=float, default=100.0,
                     help="utterance mode: a service call starts when --service-batch utterances are pending or the "
                          "oldest has waited this long")

@@ -150,6 +150,43 @@ def oracle_parity(args, enc, clips: np.ndarray, gpu_tokens, gpu_tags: np.ndarray
                     "oracle margin <= margin_tol (bf16 vs fp32 near-tie), after which free-running histories differ"}
 
 
+def _one_window_single_thread(job):
+    """Worker of cpu_process_parallel: one window, one torch thread, whole STT leg."""
+    model, seconds, sr, max_new, idx = job
+    import torch
+    torch.set_num_threads(1)
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import PRESETS, tokenizer_spec
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle import whisper_ref as R
+    from oracle.logmel_ref import log_mel_window
+    dims = PRESETS[model]
+    spec = tokenizer_spec(dims)
+    W = init_random_weights(dims, seed=0, profile="confident")
+    clip = make_clips(1, seconds, sr, seed=1234, first=idx).numpy()[0]
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        mel = torch.from_numpy(log_mel_window(clip, dims.n_mels))[None]
+        R.greedy_decode(W, dims, spec, R.encode(W, dims, mel), max_new, vectorized=True)
+    return time.perf_counter() - t0
+
+
+def cpu_process_parallel(args, cores: int) -> dict:
+    """A second CPU figure for the STT leg: `cores` independent single-threaded processes,
+    one window each -- the layout a CPU deployment of the reference would use for many streams -- instead of one
+    multi-threaded batched call. Measured once per reference run, not per step."""
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    jobs = [(args.model, args.clip_seconds, args.sample_rate, args.max_new_tokens, i) for i in range(cores)]
+    t0 = time.perf_counter()
+    with ctx.Pool(cores) as pool:
+        per = pool.map(_one_window_single_thread, jobs, chunksize=1)
+    wall = time.perf_counter() - t0
+    busy = max(per)    # the windows run concurrently: throughput = windows / slowest worker (start-up excluded)
+    return {"layout": f"{cores} single-threaded processes, one window each (greedy only; start-up excluded)",
+            "stt_audio_s_per_s": cores * args.clip_seconds / busy, "slowest_worker_s": busy, "wall_incl_startup_s": wall}
+
+
 def run_reference_stt(args) -> None:
     if int(os.environ.get("RANK", "0")) != 0:
         return
@@ -175,7 +212,8 @@ def run_reference_stt(args) -> None:
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": stt_config(args, n),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                         "probe": probe, **detail},
+                         "probe": probe, **detail,
+                         "stt_process_parallel": None if getattr(args, "beam", 0) else cpu_process_parallel(args, cores)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}), flush=True)
 
@@ -219,8 +257,7 @@ def run_gpu_stt(args) -> None:
     enc = SemanticEncoder(args.model, batch=B, max_new_tokens=args.max_new_tokens, device=dev,
                           prosody_sample_rate=sr, input_sample_rate=sr, lane_batch=args.lane_batch,
                           n_lanes=args.lanes or None, steps_per_graph=args.steps_per_graph,
-                          enc_chunk=getattr(args, "enc_chunk", 64), beam=getattr(args, "beam", 0),
-                          pace_encoder=getattr(args, "pace_encoder", False))
+                          enc_chunk=getattr(args, "enc_chunk", 64), beam=getattr(args, "beam", 0))
     beam = max(getattr(args, "beam", 0), 1)
     N = int(round(seconds * sr))
     x = make_clips(B, seconds, sr, seed=1234 + 100003 * rank, device=dev, chunk=64).reshape(-1)

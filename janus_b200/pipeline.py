@@ -115,7 +115,7 @@ class SemanticEncoder:
                  device=None, seed: int = 0, weights: dict | None = None, weight_profile: str = "confident",
                  prosody_sample_rate: int = 16000, input_sample_rate: int = 16000, lane_batch: int = 64,
                  n_lanes: int | None = None, steps_per_graph: int = 10, light: bool | None = None,
-                 enc_chunk: int = 64, latent: bool | None = None, beam: int = 0, pace_encoder: bool = False) -> None:
+                 enc_chunk: int = 64, latent: bool | None = None, beam: int = 0) -> None:
         self.dims = PRESETS[model] if isinstance(model, str) else model
         self.spec = tokenizer_spec(self.dims)
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -137,11 +137,6 @@ class SemanticEncoder:
         self.latent = latent
         self.light = (self.lane_batch <= 64 and not latent and not beam) if light is None else light
         self.max_new_tokens, self.steps_per_graph = max_new_tokens, steps_per_graph
-        # pace_encoder: encoder micro-batch i of a lane may only start once the PREVIOUSLY enqueued lane's decode has
-        # passed the matching fraction of its graph replays, so the tensor-heavy encoder is spread over the HBM-bound
-        # decode of the lane before it instead of running as one sustained burst (a power-cap experiment)
-        self.pace_encoder = pace_encoder
-        self._pace_marks: list = []
         self.decim = input_sample_rate // 16000
         assert input_sample_rate in (16000, 48000)
         d = self.dims
@@ -214,12 +209,8 @@ class SemanticEncoder:
         """K1 + K2 over one lane's windows in encoder micro-batches; fills `out` (a latent decode session's own
         encoder-state buffer) or the shared self.enc_out [lane_batch, n_ctx, d]."""
         enc_out = self.enc_out if out is None else out
-        marks = self._pace_marks if self.pace_encoder else []
-        n_chunks = -(-self.lane_batch // self.enc_chunk)
-        for ci, c0 in enumerate(range(0, self.lane_batch, self.enc_chunk)):
+        for c0 in range(0, self.lane_batch, self.enc_chunk):
             n = min(self.enc_chunk, self.lane_batch - c0)
-            if marks and ci > 0:
-                torch.cuda.current_stream(self.device).wait_event(marks[min(len(marks) - 1, ci * len(marks) // n_chunks)])
             self.whisper.frontend(pcm, offs[c0:c0 + n], lens[c0:c0 + n], decim=self.decim, scratch=self.mel_scratch[:n],
                                   out_bf16=self.mel_pad[:n])
             self.whisper.encode(self.mel_pad[:n], out=enc_out[c0:c0 + n])
@@ -258,17 +249,7 @@ class SemanticEncoder:
                 lane.stream.wait_event(lane.ready)
                 ses = lane.session
                 ses.reset()
-                if self.pace_encoder:
-                    marks: list = []
-
-                    def mark(marks=marks, st=lane.stream):
-                        ev = torch.cuda.Event()
-                        ev.record(st)
-                        marks.append(ev)
-                    ses.run_steps(after_replay=mark)
-                    self._pace_marks = marks
-                else:
-                    ses.run_steps()
+                ses.run_steps()
                 r = slice(j * lb, (j + 1) * lb)
                 if ses.beam:
                     best_tok, best_lp = ses.finalize()

@@ -45,6 +45,7 @@ from ..whisper.weights import init_random_weights, load_weights
 
 logger = logging.getLogger(__name__)
 
+STEP_BLOCK = 8                # decode steps per CUDA-graph replay / between two end-of-text checks
 MAX_NEW_TOKENS = 448          # faster-whisper: max_length=448 (DecodeSession caps at 448 - len(prompt))
 _CAPTURE_LOCK = threading.Lock()   # CUDA-graph capture of any Transcriber in this process is serialised
 
@@ -125,6 +126,9 @@ class Transcriber:
             if base:
                 with _CAPTURE_LOCK:
                     s._ensure_graph()
+                    # single steps until <|startoftranscript|> has been consumed (no_speech_prob is read there), then
+                    # STEP_BLOCK steps per replay: an utterance is launch-latency bound, fewer host launches help
+                    s.block_graph = s.capture(STEP_BLOCK) if not s.beam else None
             self._sessions[key] = s
         return s
 
@@ -136,14 +140,23 @@ class Transcriber:
         ses.cross_kv(enc)
         ses.reset()
         nsp = None
-        for step in range(ses.n_steps):   # stop as soon as the window has emitted <|endoftext|>
-            if ses.graph is not None:
-                ses.graph.replay()
+        block = getattr(ses, "block_graph", None)
+        step = 0
+        while step < ses.n_steps:   # stop as soon as the window has emitted <|endoftext|>
+            if block is not None and step > ses.sot_index and ses.n_steps - step >= STEP_BLOCK:
+                block.replay()
+                step += STEP_BLOCK
+                check = True
             else:
-                ses._step()
-            if step == ses.sot_index:
-                nsp = ses.no_speech_prob()
-            if step % 8 == 7 and step >= ses.n_prompt and int(ses.n_done.item()) >= 1:
+                if ses.graph is not None:
+                    ses.graph.replay()
+                else:
+                    ses._step()
+                if step == ses.sot_index:
+                    nsp = ses.no_speech_prob()
+                step += 1
+                check = step % STEP_BLOCK == 0
+            if check and step > ses.n_prompt and int(ses.n_done.item()) >= 1:
                 break
         if ses.beam:
             tok, lp = ses.finalize()

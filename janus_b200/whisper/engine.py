@@ -414,25 +414,30 @@ class DecodeSession:
         self.reset()
         self._step()  # eager warm-up: sets kernel attributes outside capture
         torch.cuda.current_stream(self.eng.device).synchronize()
-        g = torch.cuda.CUDAGraph()
-        # thread_local: another service thread (the reference runs STT and prosody from a 2-worker pool) may call
-        # cudaMalloc / pin memory while this thread captures
-        with torch.cuda.graph(g, capture_error_mode="thread_local"):
-            for _ in range(self.steps_per_graph):
-                self._step()
-        self.graph = g
+        self.graph = self.capture(self.steps_per_graph)
         rem = self.n_steps % self.steps_per_graph
         if rem:
-            t = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(t, capture_error_mode="thread_local"):
-                for _ in range(rem):
-                    self._step()
-            self.tail_graph = t
+            self.tail_graph = self.capture(rem)
 
     @on_device
-    def run_steps(self, n_steps: int | None = None, after_replay=None) -> None:
-        """Enqueues n_steps decode steps (default: all) on the current stream. `after_replay()` (optional) is called
-        after every graph replay has been enqueued (the engine records pacing events there)."""
+    def capture(self, n_steps: int) -> torch.cuda.CUDAGraph:
+        """A CUDA graph of `n_steps` decode steps (the step reads its position from device memory, so graphs of
+        different lengths can be mixed freely). Call after one eager step (kernel attributes are set outside capture)."""
+        g = torch.cuda.CUDAGraph()
+        # an explicit capture stream ON THIS ENGINE'S DEVICE: torch.cuda.graph's default capture stream is a class-level
+        # singleton created on whichever device was current first (a second engine on cuda:1 captured an empty graph)
+        if getattr(self, "_cap_stream", None) is None:
+            self._cap_stream = torch.cuda.Stream(self.eng.device)
+        # thread_local: another service thread (the reference runs STT and prosody from a 2-worker pool) may call
+        # cudaMalloc / pin memory while this thread captures
+        with torch.cuda.graph(g, stream=self._cap_stream, capture_error_mode="thread_local"):
+            for _ in range(n_steps):
+                self._step()
+        return g
+
+    @on_device
+    def run_steps(self, n_steps: int | None = None) -> None:
+        """Enqueues n_steps decode steps (default: all) on the current stream."""
         n = self.n_steps if n_steps is None else n_steps
         if self.graph is None:
             for _ in range(n):
@@ -441,8 +446,6 @@ class DecodeSession:
         full, rem = divmod(n, self.steps_per_graph)
         for _ in range(full):
             self.graph.replay()
-            if after_replay is not None:
-                after_replay()
         if rem:
             if rem == self.n_steps % self.steps_per_graph and self.tail_graph is not None:
                 self.tail_graph.replay()

@@ -191,3 +191,31 @@ def test_transcriber_beam_size_5_matches_oracle_beam_search(monkeypatch):
     # greedy and beam transcribers are independent objects with the reference's zero-argument construction
     with pytest.raises(ValueError):
         T.Transcriber('tiny', beam_size=9)
+
+
+def test_rich_prosody_fields_filled_from_the_device():
+    """`avg_pitch_hz` / `avg_energy` -- fields the reference's receiver reads but its sender leaves
+    None (engine.py:231-233,554-560) -- come off the device with the step's results (EncodeResult.mean_f0 / rms) and
+    equal the oracle's mean voiced f0 (numpy's pairwise float32 mean, bit for bit) and RMS (<= 1e-6 relative)."""
+    from janus_b200.pipeline import SemanticEncoder
+    from janus_b200.protocol import JanusPacket
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import mini_dims
+    from janus_b200.whisper.weights import init_random_weights
+    from oracle.prosody_oracle import ProsodyOracle
+    dims = mini_dims(d=128, heads=2, layers=2)
+    W = init_random_weights(dims, seed=3, profile="confident")
+    enc = SemanticEncoder(dims, batch=3, max_new_tokens=8, weights=W)
+    clips = make_clips(3, 10.0, 16000, seed=55).numpy()
+    bufs = [clips[0], clips[1][:70001], np.zeros(20000, np.float32)]          # the last one: nothing voiced
+    texts, pkts = enc.encode_host(bufs, timestamps=[1.0, 2.0, 3.0], rich_prosody=True)
+    plain_texts, plain_pkts = enc.encode_host(bufs, timestamps=[1.0, 2.0, 3.0])
+    for i, b in enumerate(bufs):
+        d = {}
+        tags = ProsodyOracle(sample_rate=16000).analyze_buffer(b, python_hop_loop=False, details=d)
+        got = JanusPacket.deserialize(pkts[i]).prosody
+        assert got['energy'] == tags['energy'] and got['pitch'] == tags['pitch']
+        want_f0 = 0.0 if d["avg_pitch"] is None else float(d["avg_pitch"])
+        assert got['avg_pitch_hz'] == want_f0, (i, got['avg_pitch_hz'], want_f0)
+        assert abs(got['avg_energy'] - float(d["rms"])) <= 1e-6 * max(1.0, float(d["rms"]))
+        assert set(JanusPacket.deserialize(plain_pkts[i]).prosody) == {'energy', 'pitch'}     # default bytes unchanged

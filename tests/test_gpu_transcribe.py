@@ -177,3 +177,30 @@ def test_voice_verify_similarity_step(tmp_path):
     assert ok and ratio == 1.0
     ok2, ratio2 = verify_transcript(transcript, "completely different words entirely")
     assert not ok2 and ratio2 == SequenceMatcher(None, transcript.lower().strip(), "completely different words entirely").ratio()
+
+
+def test_services_called_concurrently_from_a_two_worker_pool(monkeypatch):
+    """The reference runs STT and prosody of an utterance from a ThreadPoolExecutor(max_workers=2)
+    (/root/reference/backend/services/engine.py:410,529-531; the CLI sender may even run two utterances at once,
+    sender_main.py:201-206). Results under concurrency equal the sequential ones, including a Transcriber constructed
+    (CUDA-graph capture) while the other thread is busy allocating pinned memory in analyze_buffer."""
+    from concurrent.futures import ThreadPoolExecutor
+    import janus_b200.services.transcriber as T
+    from janus_b200.services.prosody import ProsodyExtractor
+    from janus_b200.synth import make_clips
+    monkeypatch.setattr(T, "MAX_NEW_TOKENS", 24)
+    clips = make_clips(4, 3.0, 48000, seed=91).numpy()
+    tr = T.Transcriber('tiny')
+    tr.max_windows = 1
+    seq_text = [tr.transcribe_buffer(c) for c in clips]
+    seq_tags = [ProsodyExtractor().analyze_buffer(c) for c in clips]       # fresh state per clip
+    with ThreadPoolExecutor(max_workers=2) as pool:
+        f_new = pool.submit(lambda: T.Transcriber('tiny'))                  # captures its graph on a worker thread ...
+        f_tags = [pool.submit(lambda c=c: ProsodyExtractor().analyze_buffer(c)) for c in clips]   # ... while these allocate
+        tr2 = f_new.result()
+        tr2.max_windows = 1
+        f_text = [pool.submit(tr.transcribe_buffer, c) for c in clips]      # two utterances in flight on one object
+        f_text2 = [pool.submit(tr2.transcribe_buffer, c) for c in clips]
+        assert [f.result() for f in f_tags] == seq_tags
+        assert [f.result() for f in f_text] == seq_text
+        assert [f.result() for f in f_text2] == seq_text
