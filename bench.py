@@ -355,6 +355,9 @@ def main() -> None:
         # beam search decodes from per-window K/V caches (55 MB per window for Whisper-small, one pass serves all beams)
         # and beam x the self-attention rows: 512-window lanes keep two lanes inside 180 GB
         args.batch = args.lane_batch = 512
+    if args.beam and args.model in ("medium", "large-v3") and not args.lanes:
+        # large-v3, beam 5, 256 windows: 63 GB of cross-K/V + 28 GB of self-K/V per lane -- one lane per GPU
+        args.lanes = 1
     if args.workload == "prosody":
         (run_reference_prosody if args.impl == "reference" else run_gpu_prosody)(args)
     else:
