@@ -168,16 +168,25 @@ class Transcriber:
         return tokens, sum_lp, float(nsp[0]) if nsp is not None else 0.0
 
     # ---- the utterance loop -------------------------------------------------------------------
-    def _transcribe(self, audio: np.ndarray, decim: int, beam_size: int | None = None,
-                    condition_on_previous_text: bool | None = None) -> str:
-        """audio: float32 at 16 kHz * decim (the kernel reads audio[::decim])."""
+    def _transcribe(self, audio: np.ndarray, decim: int, **overrides) -> str:
+        return self._run(audio, decim, **overrides)[0]
+
+    def _run(self, audio: np.ndarray, decim: int, beam_size: int | None = None,
+             condition_on_previous_text: bool | None = None, no_speech_threshold: float | None = None,
+             log_prob_threshold: float | None = None):
+        """audio: float32 at 16 kHz * decim (the kernel reads audio[::decim]) -> (text, segments, per-window trace).
+        The keyword arguments override the object's settings for this call only (the faster_whisper shim passes
+        transcribe()'s arguments through them); the returned lists belong to this call (race-free under the
+        reference's 2-worker pool), `last_trace` / `last_segments` are diagnostics of the most recent call."""
         beam_size = self.beam_size if beam_size is None else beam_size
+        nst = self.no_speech_threshold if no_speech_threshold is None else no_speech_threshold
+        lpt = self.log_prob_threshold if log_prob_threshold is None else log_prob_threshold
         if not 1 <= beam_size <= 8:
             raise ValueError("beam_size must be in 1 .. 8")
         cond = self.condition_on_previous_text if condition_on_previous_text is None else condition_on_previous_text
-        self.last_trace, self.last_segments = [], []
         if audio.size == 0:
-            return ''
+            self.last_trace, self.last_segments = [], []
+            return '', [], []
         spec, fe, dev = self.spec, self.model.frontend, self.model.device
         tb, eot = spec.timestamp_begin, spec.eot
         n_frames = fe.n_frames(len(audio), decim)
@@ -200,7 +209,7 @@ class Transcriber:
                     prompt = [spec.sot_prev] + all_tokens[-(spec.max_length // 2 - 1):] + prompt
                 tokens, sum_lp, nsp = self._decode_window(enc, prompt, beam_size)
                 avg_logprob = sum_lp / (len(tokens) + 1)
-                skip = nsp > self.no_speech_threshold and not avg_logprob > self.log_prob_threshold
+                skip = nsp > nst and not avg_logprob > lpt
                 trace.append({"seek": seek, "tokens": tokens, "no_speech_prob": nsp, "avg_logprob": avg_logprob,
                               "skipped": skip, "n_prompt": len(prompt)})
                 if skip:
@@ -219,7 +228,7 @@ class Transcriber:
                 seek += advance
                 all_tokens.extend(tokens)
         self.last_trace, self.last_segments = trace, segments
-        return join_segments(texts)
+        return join_segments(texts), segments, trace
 
     def transcribe_buffer(self, audio_buffer) -> str:
         if isinstance(audio_buffer, list):                      # transcriber.py:42-43
@@ -235,22 +244,28 @@ class Transcriber:
         """The reference lets faster-whisper decode any container through PyAV/FFmpeg
         (transcriber.py:66-91); neither exists here, so PCM WAV (8/16/32-bit, any rate that is a
         multiple of 16 kHz... in practice 16 or 48 kHz) is read directly and anything else raises."""
-        with wave.open(file_path, 'rb') as wf:
-            sr, ch, sw, n = wf.getframerate(), wf.getnchannels(), wf.getsampwidth(), wf.getnframes()
-            raw = wf.readframes(n)
-        if sw == 2:
-            x = np.frombuffer(raw, dtype='<i2').astype(np.float32) / 32768.0
-        elif sw == 4:
-            x = np.frombuffer(raw, dtype='<i4').astype(np.float32) / 2147483648.0
-        elif sw == 1:
-            x = (np.frombuffer(raw, dtype=np.uint8).astype(np.float32) - 128.0) / 128.0
-        else:
-            raise ValueError(f"unsupported WAV sample width {sw}")
-        if ch > 1:
-            x = x.reshape(-1, ch).mean(axis=1).astype(np.float32)
-        if sr % 16000 != 0:
-            raise ValueError(f"unsupported WAV sample rate {sr} (need a multiple of 16 kHz)")
-        return self._transcribe(x, decim=sr // 16000)
+        x, decim = read_wav(file_path)
+        return self._transcribe(x, decim=decim)
+
+
+def read_wav(file_path: str):
+    """PCM WAV -> (mono float32 samples, decimation factor to 16 kHz)."""
+    with wave.open(file_path, 'rb') as wf:
+        sr, ch, sw, n = wf.getframerate(), wf.getnchannels(), wf.getsampwidth(), wf.getnframes()
+        raw = wf.readframes(n)
+    if sw == 2:
+        x = np.frombuffer(raw, dtype='<i2').astype(np.float32) / 32768.0
+    elif sw == 4:
+        x = np.frombuffer(raw, dtype='<i4').astype(np.float32) / 2147483648.0
+    elif sw == 1:
+        x = (np.frombuffer(raw, dtype=np.uint8).astype(np.float32) - 128.0) / 128.0
+    else:
+        raise ValueError(f"unsupported WAV sample width {sw}")
+    if ch > 1:
+        x = x.reshape(-1, ch).mean(axis=1).astype(np.float32)
+    if sr % 16000 != 0:
+        raise ValueError(f"unsupported WAV sample rate {sr} (need a multiple of 16 kHz)")
+    return x, sr // 16000
 
 
 def split_window_segments(tokens: list[int], timestamp_begin: int, segment_size: int):

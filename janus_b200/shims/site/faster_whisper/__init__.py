@@ -33,22 +33,18 @@ class WhisperModel:
         tr = self._tr
         if task != "transcribe":
             raise ValueError("faster_whisper shim: only task='transcribe' is on the Janus path")
-        tr.no_speech_threshold = no_speech_threshold
-        tr.log_prob_threshold = log_prob_threshold
+        opts = dict(beam_size=beam_size, condition_on_previous_text=condition_on_previous_text,
+                    no_speech_threshold=no_speech_threshold, log_prob_threshold=log_prob_threshold)
         if isinstance(audio, str):
-            with __import__("wave").open(audio, "rb") as wf:     # validate early: same errors as transcribe_file
-                duration = wf.getnframes() / float(wf.getframerate())
-            tr.condition_on_previous_text = condition_on_previous_text
-            saved, tr.beam_size = tr.beam_size, beam_size
-            try:
-                tr.transcribe_file(audio)
-            finally:
-                tr.beam_size = saved
+            from janus_b200.services.transcriber import read_wav
+            x, decim = read_wav(audio)                                   # PCM WAV only (no PyAV / FFmpeg here)
+            duration = len(x) / (16000.0 * decim)
+            _, segments, _ = tr._run(x, decim=decim, **opts)
         else:
             audio = np.asarray(audio, dtype=np.float32).reshape(-1)       # 16 kHz mono, as faster-whisper expects
             duration = len(audio) / 16000.0
-            tr._transcribe(audio, decim=1, beam_size=beam_size, condition_on_previous_text=condition_on_previous_text)
+            _, segments, _ = tr._run(audio, decim=1, **opts)
         segs = [Segment(s["id"], s["seek"], s["start"], s["end"], s["text"], s["tokens"], s["avg_logprob"], None,
-                        s["no_speech_prob"], None, s["temperature"]) for s in tr.last_segments]
+                        s["no_speech_prob"], None, s["temperature"]) for s in segments]
         info = TranscriptionInfo(language or "en", 1.0, duration, duration, None, None, None)
         return iter(segs), info

@@ -35,11 +35,14 @@ def _env(ref):
 def test_reference_test_suite_passes_over_the_shims(tmp_path):
     """backend/tests/test_input_processing.py (TestProsodyExtractor :436-505 runs REAL numerics through the YIN
     kernel; TestTranscriber :372-429; TestSenderMain :512-694), test_transport_layer.py, test_e2e_local.py,
-    test_engine.py -- as the reference ships them."""
+    test_engine.py, test_api_flow.py, test_synthesis.py, test_voice_cloning.py -- as the reference ships them (58 tests)."""
     ref = _ref_root()
     tests = os.path.join(ref, "backend", "tests")
-    files = [os.path.join(tests, f) for f in ("test_input_processing.py", "test_transport_layer.py",
-                                              "test_e2e_local.py", "test_engine.py")]
+    # every test module the reference ships (hardware_check.py / manual_sender.py are manual scripts, not tests):
+    # test_api_flow.py constructs the real `Transcriber()` in the FastAPI lifespan -- over the shim that is the B200 path
+    files = [os.path.join(tests, f) for f in ("test_input_processing.py", "test_transport_layer.py", "test_e2e_local.py",
+                                              "test_engine.py", "test_api_flow.py", "test_synthesis.py",
+                                              "test_voice_cloning.py")]
     log = tmp_path / "maps.txt"
     # a tiny plugin: at session end, record which shared objects of this repo the pytest process has mapped
     plugin = tmp_path / "janus_maps_plugin.py"
@@ -54,7 +57,7 @@ def test_reference_test_suite_passes_over_the_shims(tmp_path):
     print(tail)
     assert r.returncode == 0, tail
     m = re.search(r"(\d+) passed", r.stdout)
-    assert m and int(m.group(1)) >= 40, tail
+    assert m and int(m.group(1)) >= 55, tail
     assert "failed" not in r.stdout.splitlines()[-1]
     assert log.exists() and "libjanus_b200.so" in log.read_text(), "the reference's tests ran without the native library"
 
