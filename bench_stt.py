@@ -443,7 +443,7 @@ def run_gpu_stt(args) -> None:
                          + 2 * (2 * Ta) * dd * 3 * d.n_mels + 2 * Ta * dd * 3 * dd)
         traffic = None   # dram bytes of one launch from the committed ncu --set full capture, if it is this launch shape
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r01_xlat_traffic.json" if latent else
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r02_xlat_traffic.json" if latent else
                                              ("r01_xattn_beam_traffic.json" if beam > 1 else "r01_xattn_traffic.json"))))
             if (tj["lane_batch"], tj["n_heads"], tj["n_ctx"], tj.get("beam", 1)) == (lb, H, T, beam):
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
