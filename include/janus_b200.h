@@ -95,6 +95,22 @@ int32_t janus_prosody_reduce_f32(const float* f0, const float* hop_sumsq, const 
                                  float* rms_out, float* mean_f0_out, int32_t* n_voiced_out,
                                  uint8_t* tags_out, void* stream);
 
+/* janus_prosody_reduce_f32 without caller-provided scratch and WITHOUT ANY ALLOCATION. This entry point has no
+ * counterpart in the reference: it was added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). The scratch of the
+ * voiced-hop compaction is a static device array of JANUS_PROSODY_STATIC_MAX_HOPS floats (4 MiB, held by every GPU
+ * that loads the library until exit). total_hops must be hop_offsets[n_streams]; a value beyond the maximum is
+ * rejected with JANUS_ERR_INVALID_ARG and a message. Results are bit-identical to janus_prosody_reduce_f32. All calls
+ * share the array (it keeps the previous call's contents; nothing needs clearing): calls that OVERLAP on the GPU --
+ * two streams, or a replayed graph running concurrently with another call -- race. The first call on a device takes
+ * the array's address (cudaGetSymbolAddress): make one call outside stream capture before capturing it. Calls no
+ * cudaMalloc / cudaFree / allocating library routine. */
+#define JANUS_PROSODY_STATIC_MAX_HOPS 1048576
+int32_t janus_prosody_reduce_static_f32(const float* f0, const float* hop_sumsq, const int64_t* hop_offsets,
+                                        const int64_t* stream_lengths, int32_t n_streams, int64_t total_hops,
+                                        float* rms_out, float* mean_f0_out, int32_t* n_voiced_out, uint8_t* tags_out,
+                                        void* stream);
+
 /* Per-chunk speech gate for many sessions, from the outputs of janus_yin_frames_f32 (the step before the path:
  * backend/services/engine.py:471-493 asks backend/services/vad.py per 1536-sample chunk; Silero's model is a download,
  * so this is an energy gate (two thresholds), NOT a reproduction of Silero's decisions). Chunk c = hops

@@ -30,6 +30,7 @@ SIGNATURES = {
                                     _P, _P, _P, _P, _P]),
     "janus_yin_state_f32": (_I32, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     "janus_prosody_reduce_f32": (_I32, [_P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _P]),
+    "janus_prosody_reduce_static_f32": (_I32, [_P, _P, _P, _P, _I32, _I64, _P, _P, _P, _P, _P]),
     "janus_vad_gate_f32": (_I32, [_P, _P, _I64, _I32, _F32, _I32, _P, _P, _P]),
     "janus_layernorm_bf16": (_I32, [_P, _P, _P, _P, _I64, _I32, _P]),
     "janus_attention_enc_bf16": (_I32, [_P, _P, _I32, _I32, _I32, _P]),

@@ -439,3 +439,42 @@ extern "C" int32_t janus_vad_gate_f32(const float* f0, const float* hop_db, int6
   JANUS_LAUNCH_CHECK("vad_gate_kernel");
   return JANUS_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// No-allocation variant of janus_prosody_reduce_f32 (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops,
+// harnesses that forbid it). The [total_hops] float scratch of the voiced-hop compaction lives in a file-scope
+// device array of JANUS_PROSODY_STATIC_MAX_HOPS floats (4 MiB; every GPU that loads the library holds it until
+// exit). In HOST code `g_prosody_scratch` is only a stand-in for the symbol, not a device address: the address is
+// taken once per device, with that device current, through cudaGetSymbolAddress and passed to the kernel.
+// Every call shares the array and it keeps the last call's contents; nothing has to start at zero (each stream's
+// segment is written by the compaction before the pairwise sum reads it), so nothing is cleared. Two calls that
+// overlap on the GPU (different streams, or a captured graph replayed concurrently with itself) race on it.
+// ------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_prosody_scratch[JANUS_PROSODY_STATIC_MAX_HOPS];
+
+extern "C" int32_t janus_prosody_reduce_static_f32(const float* f0, const float* hop_sumsq, const int64_t* hop_offsets,
+                                                   const int64_t* stream_lengths, int32_t n_streams,
+                                                   int64_t total_hops, float* rms_out, float* mean_f0_out,
+                                                   int32_t* n_voiced_out, uint8_t* tags_out, void* stream) {
+  if (n_streams <= 0) return JANUS_OK;
+  JANUS_CHECK_ARG(f0 && hop_sumsq && hop_offsets && stream_lengths, "prosody_reduce_static: null input pointer");
+  JANUS_CHECK_ARG(rms_out && mean_f0_out && n_voiced_out && tags_out, "prosody_reduce_static: null output pointer");
+  JANUS_CHECK_ARG(total_hops >= 0, "prosody_reduce_static: negative total_hops");
+  JANUS_CHECK_ARG(total_hops <= (int64_t)JANUS_PROSODY_STATIC_MAX_HOPS,
+                  "prosody_reduce_static: total_hops=%lld exceeds the static scratch of %lld hops "
+                  "(JANUS_PROSODY_STATIC_MAX_HOPS); use janus_prosody_reduce_f32 with caller-provided scratch",
+                  (long long)total_hops, (long long)JANUS_PROSODY_STATIC_MAX_HOPS);
+  static float* dev_ptr[64] = {};   // per device: the array has a different address on every GPU
+  const int dev = current_device_slot();
+  if (!dev_ptr[dev]) {
+    float* ptr = nullptr;
+    JANUS_CUDA(cudaGetSymbolAddress((void**)&ptr, g_prosody_scratch));
+    dev_ptr[dev] = ptr;
+  }
+  const int wpb = 4;
+  prosody_reduce_kernel<<<(n_streams + wpb - 1) / wpb, wpb * 32, 0, (cudaStream_t)stream>>>(
+      f0, hop_sumsq, hop_offsets, stream_lengths, n_streams, dev_ptr[dev], rms_out, mean_f0_out, n_voiced_out, tags_out);
+  JANUS_LAUNCH_CHECK("prosody_reduce_kernel (static scratch)");
+  return JANUS_OK;
+}
