@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define JANUS_ABI_VERSION 1
+#define JANUS_ABI_VERSION 2   /* 2: janus_set_option replaces janus_set_pdl; debug exports and the fused-segment flag retired */
 
 typedef enum {
   JANUS_OK = 0,

@@ -55,6 +55,8 @@ SIGNATURES = {
 }
 
 
+ABI_VERSION = 2   # JANUS_ABI_VERSION of include/janus_b200.h these bindings were written against
+
 # janus_option_t (include/janus_b200.h)
 OPT_PDL, OPT_ATT_SPLIT, OPT_XLAT_STREAM, OPT_XLAT_CTAS, OPT_XA_CTAS_PER_SM, OPT_BEAM_SHARED_SELF_ATTN = range(6)
 
@@ -96,8 +98,9 @@ def lib() -> ctypes.CDLL:
             fn = getattr(L, name)  # AttributeError if the symbol is not exported
             fn.restype = res
             fn.argtypes = args
-        if L.janus_abi_version() != 1:
-            raise JanusNativeError("libjanus_b200.so ABI version mismatch")
+        if L.janus_abi_version() != ABI_VERSION:
+            raise JanusNativeError(f"libjanus_b200.so ABI version {L.janus_abi_version()} != {ABI_VERSION} expected by "
+                                   "janus_b200/_abi.py: rebuild with `python -m janus_b200.build --force`")
         _lib = L
     return _lib
 

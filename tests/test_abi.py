@@ -24,7 +24,7 @@ def test_library_builds_and_loads():
     path = jbuild.build()
     assert os.path.exists(path)
     lib = _abi.lib()
-    assert lib.janus_abi_version() == 1
+    assert lib.janus_abi_version() == _abi.ABI_VERSION == 2
     assert lib.janus_yin_frames_per_group() >= 1
 
 
