@@ -204,3 +204,24 @@ def test_services_called_concurrently_from_a_two_worker_pool(monkeypatch):
         assert [f.result() for f in f_tags] == seq_tags
         assert [f.result() for f in f_text] == seq_text
         assert [f.result() for f in f_text2] == seq_text
+
+
+@pytest.mark.parametrize("n48", [100, 479, 1440000, 1440003, 1441500])
+def test_window_boundary_lengths_match_the_oracle_loop(monkeypatch, n48):
+    """Edge lengths of the utterance loop: shorter than one feature frame (no window at all -> ''), a single content frame, exactly 30 s
+    (content_frames = 3000: one full window), 30 s + 1 sample at 16 kHz (still 3000 content frames) and 30.03 s (a second
+    window whose seek depends on the first window's timestamps)."""
+    from janus_b200.synth import make_clips
+    from janus_b200.whisper.config import detokenize
+    from oracle.transcribe_ref import transcribe
+    tr, W = _mk(monkeypatch, max_new=16)
+    tr.max_windows = 2
+    x48 = make_clips(1, 31.0, 48000, seed=97).numpy()[0][:n48]
+    text = tr.transcribe_buffer(x48)
+    trace = []
+    ref = transcribe(W, tr.dims, tr.spec, x48[::3], lambda ids: detokenize(ids, tr.spec), max_new_tokens=16, trace=trace,
+                     max_windows=2)
+    assert [(t["seek"], t["tokens"]) for t in tr.last_trace] == [(t["seek"], t["tokens"]) for t in trace]
+    assert text == ref
+    if n48 == 100:       # 34 samples at 16 kHz: zero content frames, the loop never runs
+        assert text == '' and tr.last_trace == []

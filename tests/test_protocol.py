@@ -80,3 +80,44 @@ def test_pack_packets_matches_serialize():
     for i in (0, 3):
         assert out[i] == JanusPacket(texts[i], JanusMode.SEMANTIC_VOICE, pros[i], "auto", ts[i]).serialize()
         assert msgpack.unpackb(out[i])['t'] == texts[i]
+
+
+def _reference_protocol():
+    """The reference's own protocol.py (mounted at /root/reference or staged, unmodified, under baseline/_ref)."""
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for base in ("/root/reference", os.path.join(root, "baseline", "_ref")):
+        path = os.path.join(base, "backend", "common", "protocol.py")
+        if os.path.exists(path):
+            spec = importlib.util.spec_from_file_location("ref_protocol_fuzz", path)
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            return mod
+    pytest.skip("reference protocol.py not available on this machine")
+
+
+def test_fuzz_against_the_reference_module():
+    """Property test (hypothesis): for arbitrary unicode text, every mode, arbitrary prosody maps (incl. the numeric
+    avg_pitch_hz / avg_energy extension), overrides ('Auto' / None / any string / a str-Enum as the server passes) and
+    float timestamps, `JanusPacket.serialize()` and `pack_packets` emit exactly the reference's bytes, and the
+    reference's deserialize reads them back."""
+    from hypothesis import given, settings, strategies as st
+    ref = _reference_protocol()
+    text = st.text(max_size=400)
+    tags = st.dictionaries(st.sampled_from(["energy", "pitch", "avg_pitch_hz", "avg_energy", "x"]),
+                           st.one_of(st.sampled_from(["Quiet", "Normal", "Loud", "Deep", "High"]),
+                                     st.floats(allow_nan=False, allow_infinity=False, width=32)), max_size=4)
+    override = st.one_of(st.none(), st.just("Auto"), st.just("auto"), st.text(max_size=12), st.just(_StrEnum.AUTO))
+    ts = st.floats(min_value=0.0, max_value=4e9, allow_nan=False)
+
+    @settings(max_examples=300, deadline=None)
+    @given(text, st.sampled_from([0, 1, 2]), tags, override, ts)
+    def check(t, m, p, o, stamp):
+        want = ref.JanusPacket(t, ref.JanusMode(m), p, o, stamp).serialize()
+        assert JanusPacket(t, JanusMode(m), p, o, stamp).serialize() == want
+        got = pack_packets([t], [p], JanusMode(m), o, [stamp], skip_empty_text=False)[0]
+        assert got == want
+        back = ref.JanusPacket.deserialize(got)
+        assert back.text == t and int(back.mode) == m and back.prosody == p and back.timestamp == stamp
+
+    check()
