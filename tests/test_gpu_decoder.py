@@ -176,7 +176,7 @@ def test_latent_session_matches_kv_session_many_windows():
     absorb / value GEMMs at real sizes): teacher-forced logits of the latent session against the K/V-cache
     session on the same encoder states. Both are bf16 pipelines that round at different places (K/V rounds the
     projected keys, latent rounds the absorbed queries): against the fp32 oracle each shows mean |logit err|
-    0.036 / max 0.4-0.55 at these shapes with "confident" weights (scripts/gpu_latent_diag.py), so against each
+    0.036 / max 0.4-0.55 at these shapes with "confident" weights (round-1 diagnostic run), so against each
     other the bound is twice that."""
     from janus_b200.whisper.config import PRESETS
     from janus_b200.whisper.engine import DecodeSession, WhisperEngine
@@ -208,7 +208,7 @@ def test_latent_session_real_presets_vs_oracle(preset):
     """Latent cross-attention at real Whisper shapes (tiny: d=384, 6 heads -> 6 boxes / 3 feature blocks per tile;
     base.en: d=512, 8 heads -- the reference's default model, transcriber.py:11) against the fp32 oracle, next to
     the K/V-cache session on the same inputs. With random weights at these depths bf16 noise moves a few argmaxes
-    even at fp32 margins of ~0.8 in BOTH formulations (scripts/gpu_latent_diag2.py), so the statement tested is:
+    even at fp32 margins of ~0.8 in BOTH formulations (round-1 diagnostic run), so the statement tested is:
     the latent path is as close to the oracle as the K/V path (mean / max logit error within 1.3x / 1.5x,
     argmax agreement within 0.1), and both stay under mean |err| 0.03."""
     from janus_b200.whisper.config import PRESETS, tokenizer_spec
