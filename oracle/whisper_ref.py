@@ -115,7 +115,7 @@ class DecoderState:
 
 
 def apply_logit_rules(logits: torch.Tensor, generated: list[int], spec: TokenizerSpec,
-                      suppress_mask: torch.Tensor) -> torch.Tensor:
+                      suppress_mask: torch.Tensor, return_gap: bool = False):
     """One sequence. `generated` = tokens sampled so far (after the sot prompt). Returns filtered
     logits (-inf = forbidden). Order follows faster-whisper / openai-whisper: SuppressBlank,
     SuppressTokens, ApplyTimestampRules."""
@@ -145,11 +145,17 @@ def apply_logit_rules(logits: torch.Tensor, generated: list[int], spec: Tokenize
     max_text = lp[:tb].max()
     if ts_lp > max_text:
         lg[:tb] = ninf
+    if return_gap:
+        # how close the rule's own decision was: |log sum p(timestamps) - max log p(text)| when both categories are
+        # open. A near-tie HERE flips the sampled token between a timestamp and a text token although the top-1 / top-2
+        # margin inside either category may be large, so the decision margin of a greedy step is the min of the two.
+        both = bool(torch.isfinite(ts_lp)) and bool(torch.isfinite(max_text))
+        return lg, (float((ts_lp - max_text).abs()) if both else float("inf"))
     return lg
 
 
 def apply_logit_rules_batch(logits: torch.Tensor, generated: list[list[int]], spec: TokenizerSpec,
-                            suppress_mask: torch.Tensor, active=None) -> torch.Tensor:
+                            suppress_mask: torch.Tensor, active=None, return_gap: bool = False):
     """apply_logit_rules() for B sequences at once (same rules, same order, as column-range masks), so that the CPU
     baseline is not dominated by a per-sequence Python loop. Checked against the scalar function on random
     histories in tests/test_oracle_stt.py. Rows with active[b] == False are returned unfiltered."""
@@ -177,6 +183,10 @@ def apply_logit_rules_batch(logits: torch.Tensor, generated: list[list[int]], sp
     ts_lp = torch.logsumexp(lp[:, tb:], dim=-1)
     max_text = lp[:, :tb].max(dim=-1).values
     lg[((ts_lp > max_text) & act)[:, None] & (col < tb)] = ninf
+    if return_gap:
+        gap = (ts_lp - max_text).abs()
+        gap[~(torch.isfinite(ts_lp) & torch.isfinite(max_text))] = float("inf")
+        return lg, gap
     return lg
 
 
@@ -190,7 +200,9 @@ def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tens
                   stop_at_eot: bool = True, return_margins: bool = False, vectorized: bool = False,
                   prompt: list | None = None, return_no_speech: bool = False):
     """Batched greedy decode at temperature 0. Returns tokens [B, max_new_tokens] (eot-padded after
-    the first eot), sum of log-probs [B], and optionally the top-1/top-2 margin at every step."""
+    the first eot), sum of log-probs [B], and optionally the DECISION MARGIN of every step: the smaller of the
+    top-1 / top-2 gap of the rule-filtered logits and the gap of the timestamps-vs-text rule decision (in
+    log-prob units) -- the amount of logit error that could change the sampled token."""
     B = enc_out.shape[0]
     st = DecoderState(W, dims, enc_out)
     sup = suppress_mask_for(spec)
@@ -211,15 +223,21 @@ def greedy_decode(W, dims: WhisperDims, spec: TokenizerSpec, enc_out: torch.Tens
     for t in range(n_steps):
         nxt = torch.full((B,), spec.eot, dtype=torch.long)
         if vectorized:   # the same rules for all rows at once (apply_logit_rules_batch)
-            lg_all = apply_logit_rules_batch(logits, gen, spec, sup, active=[not d_ for d_ in done])
+            lg_all, gap_all = apply_logit_rules_batch(logits, gen, spec, sup, active=[not d_ for d_ in done],
+                                                      return_gap=True)
         for b in range(B):
             if done[b]:
                 continue
-            lg = lg_all[b] if vectorized else apply_logit_rules(logits[b], gen[b], spec, sup)
+            if vectorized:
+                lg, gap = lg_all[b], float(gap_all[b])
+            else:
+                lg, gap = apply_logit_rules(logits[b], gen[b], spec, sup, return_gap=True)
             lp = torch.log_softmax(lg, dim=-1)
             top2 = torch.topk(lg, 2)
             tok = int(top2.indices[0])
-            margins[b, t] = float(top2.values[0] - top2.values[1])
+            # decision margin of this step: top-1 vs top-2 of the filtered logits, or the gap of the
+            # "timestamps outweigh text" rule itself, whichever is smaller
+            margins[b, t] = min(float(top2.values[0] - top2.values[1]), gap)
             nxt[b] = tok
             out[b, t] = tok
             sum_lp[b] += lp[tok]

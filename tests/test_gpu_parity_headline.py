@@ -13,8 +13,13 @@ the same (bf16-representable) random-init weights, "confident" profile:
                       that position is <= MARGIN_TOL (a near-tie that bf16 rounding may legitimately resolve either
                       way: north_star's "bit-exact greedy tokens" is only well-defined away from ties)
 
-MARGIN_TOL is stated in logit units next to the measured bf16 logit error of the same run (printed). Every test prints
-the minimum oracle margin it ran at, so the statement can be seen not to be vacuous.
+"Margin" is the oracle's DECISION margin of a greedy step (oracle/whisper_ref.greedy_decode): the smaller of the top-1 /
+top-2 gap of the rule-filtered logits and the gap of the "timestamps outweigh text" rule decision itself
+(|log sum p(timestamps) - max log p(text)|) -- a near-tie in that rule flips the token between the two categories even
+when the gap inside either category is large (found by checking 32 windows of the bench batch: two windows diverged at
+top-1 / top-2 gaps of 0.7 and 1.5 because the rule's own decision was a near-tie). MARGIN_TOL is stated in logit units
+next to the measured bf16 logit error of the same run (printed). Every test prints the minimum oracle margin it ran at,
+so the statement can be seen not to be vacuous.
 """
 import numpy as np
 import pytest
