@@ -137,8 +137,15 @@ def run_utterance_mode(args) -> None:
         on_time = lateness[-1] < tick_s
         if pending and (len(pending) >= Bq or t == n_ticks - 1 or
                         (on_time and now() - pending_arr[0] >= args.max_wait_ms / 1e3)):
-            items, arr = pending[:Bq], pending_arr[:Bq]
-            pending, pending_arr = pending[Bq:], pending_arr[Bq:]
+            # at most one utterance per session and call: the session's YIN state is carried from one utterance to the
+            # next, so a second utterance of the same session (possible under backlog) waits for the next call
+            items, arr, rest, rest_arr, seen = [], [], [], [], set()
+            for it, a in zip(pending, pending_arr):
+                if len(items) < Bq and it[0] not in seen:
+                    seen.add(it[0]); items.append(it); arr.append(a)
+                else:
+                    rest.append(it); rest_arr.append(a)
+            pending, pending_arr = rest, rest_arr
             ts = now()
             l, k = service(items, arr, now)
             svc_time += now() - ts
