@@ -343,7 +343,7 @@ def main() -> None:
     ap.add_argument("--streams", type=int, default=4096, help="streams per GPU (prosody workload)")
     ap.add_argument("--clip-seconds", type=float, default=30.0)
     ap.add_argument("--sample-rate", type=int, default=16000)
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=8, help="end-to-end steps timed (capped by --steps)")
     ap.add_argument("--cpu-clips", type=int, default=0)
     ap.add_argument("--ref-clips", type=int, default=0)
     ap.add_argument("--ref-windows", type=int, default=2, help="windows per CPU reference step (stt_prosody)")
